@@ -1,0 +1,233 @@
+/*
+ * nums_b200.h — C ABI of libnumsb200.so, the sm_100a block-compute library behind
+ * the NumS `Backend` + kernel-module plug-in (nums_b200.cuda_backend / cuda_kernel).
+ *
+ * Conventions
+ *   - Every pointer named *_d / documented "device" is a raw device pointer on `device`
+ *     (e.g. torch.Tensor.data_ptr()).  No torch / C++ types cross this boundary.
+ *   - Every entry point selects `device`, enqueues its work on `stream`
+ *     (a cudaStream_t passed as void*; NULL = legacy default stream) and returns
+ *     without synchronising unless stated.  Return value: 0 = ok, non-zero = error;
+ *     nb_last_error() returns the thread-local message.
+ *   - Arrays are C-contiguous unless strides are passed.  Strides are in ELEMENTS.
+ *   - Kernels that need scratch take (scratch, scratch_bytes) from the caller; the
+ *     matching *_scratch_bytes() query tells how much.  The library never allocates
+ *     device memory.
+ *
+ * Each declaration cites the reference (nums-project/nums v0.2.8) interface it replaces.
+ */
+#ifndef NUMS_B200_H
+#define NUMS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* element types of a block (nums/core/kernel/numpy_kernel.py works on np.ndarray of these) */
+typedef enum {
+  NB_F64 = 0,
+  NB_I64 = 1,
+  NB_BOOL = 2, /* 1 byte, 0/1 */
+  NB_F32 = 3,  /* astype only */
+  NB_I32 = 4   /* astype only */
+} nb_dtype;
+
+/* binary ufuncs reachable through KernelCls.bop (numpy_kernel.py:414-431, settings.py:50-63) */
+typedef enum {
+  NB_ADD = 0, NB_SUB, NB_MUL, NB_TRUEDIV, NB_FLOORDIV, NB_MOD, NB_FMOD, NB_POW, NB_FLOAT_POW,
+  NB_MAXIMUM, NB_MINIMUM, NB_FMAX, NB_FMIN,
+  NB_LT, NB_LE, NB_GT, NB_GE, NB_EQ, NB_NE,
+  NB_LOGICAL_AND, NB_LOGICAL_OR, NB_LOGICAL_XOR,
+  NB_BIT_AND, NB_BIT_OR, NB_BIT_XOR, NB_LSHIFT, NB_RSHIFT,
+  NB_ARCTAN2, NB_HYPOT, NB_COPYSIGN, NB_NEXTAFTER, NB_LDEXP, NB_HEAVISIDE,
+  NB_LOGADDEXP, NB_LOGADDEXP2, NB_GCD, NB_LCM, NB_XLOGY,
+  NB_BOP_COUNT
+} nb_bop_code;
+
+/* unary ufuncs reachable through KernelCls.map_uop (numpy_kernel.py:316-318) */
+typedef enum {
+  NB_ABS = 0, NB_NEGATIVE, NB_POSITIVE, NB_SIGN, NB_SQUARE, NB_RECIPROCAL, NB_SQRT, NB_CBRT,
+  NB_EXP, NB_EXP2, NB_EXPM1, NB_LOG, NB_LOG2, NB_LOG10, NB_LOG1P,
+  NB_SIN, NB_COS, NB_TAN, NB_ARCSIN, NB_ARCCOS, NB_ARCTAN,
+  NB_SINH, NB_COSH, NB_TANH, NB_ARCSINH, NB_ARCCOSH, NB_ARCTANH,
+  NB_CEIL, NB_FLOOR, NB_TRUNC, NB_RINT, NB_DEG2RAD, NB_RAD2DEG,
+  NB_ISNAN, NB_ISINF, NB_ISFINITE, NB_SIGNBIT, NB_LOGICAL_NOT, NB_INVERT, NB_SPACING,
+  NB_UOP_COUNT
+} nb_uop_code;
+
+/* reductions reachable through KernelCls.reduce_axis / bop_reduce (numpy_kernel.py:294-313,433-453) */
+typedef enum {
+  NB_RSUM = 0, NB_RPROD, NB_RMIN, NB_RMAX, NB_RALL, NB_RANY, NB_RNANSUM, NB_RNANMIN, NB_RNANMAX,
+  NB_RED_COUNT
+} nb_red_code;
+
+/* GLM families of nums/models/glms.py */
+typedef enum {
+  NB_GLM_LINEAR = 0,   /* LinearRegressionBase  glms.py:275-327 */
+  NB_GLM_LOGISTIC = 1, /* LogisticRegression    glms.py:430-512 */
+  NB_GLM_POISSON = 2   /* PoissonRegression     glms.py:515-556 */
+} nb_glm_family;
+
+/* ---- library ------------------------------------------------------------------------- */
+
+/* Thread-local message of the last failing call ("" if none). */
+const char* nb_last_error(void);
+/* ABI version (bumped on any signature change). */
+int nb_version(void);
+/* Number of visible CUDA devices; <0 on error.  Replaces Backend.devices() discovery
+ * (nums/core/backends/serial.py:44, ray.py:55-125). */
+int nb_device_count(void);
+/* Fills sm_count / compute capability of `device`. */
+int nb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- elementwise: KernelCls.bop (non-tensordot branch), numpy_kernel.py:426-431 -------- */
+
+/* out[idx] = op(a[idx], b[idx]) with NumPy broadcasting expressed as strides.
+ * ndim <= 4; shape[] is the broadcast output shape; sa[]/sb[] are element strides of the
+ * operands in that shape (0 on broadcast axes; deferred transposes a1_T/a2_T are just swapped
+ * strides).  `cdt` is the type the ufunc loop computes in (NumPy's common type: NB_F64, NB_I64
+ * or NB_BOOL); `odt` the dtype NumPy returns (decided on the host exactly like
+ * nums/core/array/utils.py:40-51).  Integer semantics follow NumPy, not C (floor division,
+ * sign of mod, x//0 == 0, shifts >= 64, wrapping power). */
+int nb_bop(int device, int op, int ndim, const int64_t* shape,
+           const void* a_d, int adt, const int64_t* sa,
+           const void* b_d, int bdt, const int64_t* sb,
+           void* out_d, int odt, int cdt, void* stream);
+
+/* ---- elementwise: KernelCls.map_uop, numpy_kernel.py:316-318 --------------------------- */
+
+/* out[i] = op(a[i]) over n contiguous elements; cdt/odt as in nb_bop. */
+int nb_uop(int device, int op, int64_t n, const void* a_d, int adt,
+           void* out_d, int odt, int cdt, void* stream);
+
+/* ---- KernelCls.where, 3-argument form, numpy_kernel.py:331-334 ------------------------- */
+int nb_where3(int device, int64_t n, const void* cond_d, int cond_dt,
+              const void* x_d, const void* y_d, void* out_d, int xdt, void* stream);
+
+/* ---- KernelCls.where, 1-argument form (np.where(arr) + block offsets), :320-330 -------- */
+
+/* Pass 1: counts non-zeros.  chunk_counts_d: int64[nb_where_chunks(n)] scratch,
+ * total_d: int64[1].  The host reads *total_d (the one sync the reference also has,
+ * application.py:634) to size the outputs. */
+int64_t nb_where_chunks(int64_t n);
+int nb_where_count(int device, int64_t n, const void* cond_d, int cond_dt,
+                   int64_t* chunk_counts_d, int64_t* total_d, void* stream);
+/* Pass 2: writes, in C order, for every non-zero element its index along each of `ndim`
+ * axes plus offsets[axis] into idx_out_d[axis] (int64[total] each; idx_out_d itself, shape and
+ * offsets are HOST arrays of length ndim <= 4).
+ * chunk_counts_d must be the array produced by nb_where_count for the same input. */
+int nb_where_fill(int device, int64_t n, const void* cond_d, int cond_dt,
+                  int ndim, const int64_t* shape, const int64_t* offsets,
+                  const int64_t* chunk_counts_d, int64_t* const* idx_out_d, void* stream);
+
+/* ---- KernelCls.astype :339, new_block :93, create_block/update_block :116-155,
+ *      transpose :343, reshape :510 (views are host-side; these are the copies) ---------- */
+int nb_astype(int device, int64_t n, const void* a_d, int adt, void* out_d, int odt, void* stream);
+int nb_fill(int device, int64_t n, void* out_d, int odt, double fvalue, int64_t ivalue, void* stream);
+/* eye(rows, cols) block with 1 on the diagonal (new_block "eye", :97-99) */
+int nb_eye(int device, int64_t rows, int64_t cols, void* out_d, int odt, void* stream);
+/* Strided N-D (<=4) copy of itemsize-byte elements: dst[idx*dstrides] = src[idx*sstrides]. */
+int nb_copy_strided(int device, int ndim, const int64_t* shape, int itemsize,
+                    const void* src_d, const int64_t* sstrides,
+                    void* dst_d, const int64_t* dstrides, void* stream);
+
+/* ---- reductions: KernelCls.reduce_axis :294-313, sum_reduce :291, bop_reduce :433-453 -- */
+
+/* Views the input as [outer, len, inner] (C order) and reduces the middle axis:
+ * out[o, i] = red_{k} a[o, k, i].  axis=None is outer=inner=1.  `acc_dt` is the accumulator
+ * type (NB_F64 for the reference's matmul(ones, arr) path on integer input, quirk Q1).
+ * Deterministic: fixed two-stage order, no atomics. */
+size_t nb_reduce_scratch_bytes(int64_t outer, int64_t len, int64_t inner);
+int nb_reduce(int device, int red, int64_t outer, int64_t len, int64_t inner,
+              const void* a_d, int adt, void* out_d, int odt, int acc_dt,
+              void* scratch_d, size_t scratch_bytes, void* stream);
+/* out = a (red) b elementwise over n elements of one dtype (pairwise tree combine). */
+int nb_bop_reduce(int device, int red, int64_t n, const void* a_d, const void* b_d,
+                  void* out_d, int dt, void* stream);
+/* out = sum of k equal-shape arrays, accumulated left to right like np.add.reduce(arrs).
+ * ptrs: HOST array of k device pointers. */
+int nb_sum_reduce(int device, int k, int64_t n, const void* const* ptrs, void* out_d, int dt,
+                  void* stream);
+
+/* ---- KernelCls.arg_op, numpy_kernel.py:492-508 ----------------------------------------- */
+
+/* (start + argmax/argmin(a), optimum) of a flat array with NumPy's NaN rule (first NaN wins),
+ * then the reference's chain rule: the earlier pair (other_idx_d, other_val_d; NULL = none) is
+ * kept only if STRICTLY better, so a later block wins ties (quirk Q2). */
+size_t nb_argop_scratch_bytes(int64_t n);
+int nb_argop(int device, int is_max, int64_t n, const void* a_d, int adt, int64_t start,
+             const int64_t* other_idx_d, const void* other_val_d,
+             int64_t* out_idx_d, void* out_val_d,
+             void* scratch_d, size_t scratch_bytes, void* stream);
+
+/* ---- KernelCls.bop "tensordot" branch, numpy_kernel.py:419-425 (np.matmul, <=2-D) ------ */
+
+/* C[m,n] = op(A)[m,k] . op(B)[k,n], float64, FP64 tensor-core (DMMA) tiles.
+ * a_rs/a_cs: element strides of op(A) along m and k (one of them must be 1);
+ * b_rs/b_cs: strides of op(B) along k and n (one of them must be 1).
+ * n == 1 / m == 1 cover mat.vec, vec.mat and dot.  `w_d` (nullable, length k) scales the
+ * contraction index: C = op(A) . diag(w) . op(B)  — the Hessian X^T.diag(s).X of
+ * glms.py:491-499 without materialising s*X.  Deterministic split-K through `scratch`. */
+size_t nb_matmul_scratch_bytes(int device, int64_t m, int64_t n, int64_t k);
+int nb_matmul_f64(int device, int64_t m, int64_t n, int64_t k,
+                  const double* a_d, int64_t a_rs, int64_t a_cs,
+                  const double* b_d, int64_t b_rs, int64_t b_cs,
+                  const double* w_d, double* c_d, int64_t ldc,
+                  void* scratch_d, size_t scratch_bytes, void* stream);
+/* Same contraction for int64 blocks (NumPy uses non-BLAS loops; wrapping arithmetic). */
+int nb_matmul_i64(int device, int64_t m, int64_t n, int64_t k,
+                  const int64_t* a_d, int64_t a_rs, int64_t a_cs,
+                  const int64_t* b_d, int64_t b_rs, int64_t b_cs,
+                  int64_t* c_d, int64_t ldc, void* stream);
+
+/* ---- KernelCls.inv, numpy_kernel.py:471-472 (np.linalg.inv) ----------------------------- */
+
+/* out = inverse of the p x p row-major matrix a (partial pivoting).  info_d: int32[1] set to
+ * 0, or k>0 if pivot k was exactly zero (singular, NumPy raises LinAlgError).
+ * scratch: nb_inv_scratch_bytes(p). */
+size_t nb_inv_scratch_bytes(int64_t p);
+int nb_inv_f64(int device, int64_t p, const double* a_d, double* out_d, int32_t* info_d,
+               void* scratch_d, size_t scratch_bytes, void* stream);
+
+/* ---- the GLM inner loop: glms.py:457-499 (Logistic), :275-327 (Linear), :515-556 (Poisson)
+ *      as called from newton() :660-676 and LBFGS lbfgs.py:102-155 ------------------------ */
+
+/* One pass over a row block X[n, d] (row stride ldx) and y[n] (NB_F64 or NB_I64) with
+ * beta[p], p = d + 1, the intercept last (GLM.fit appends a ones column, glms.py:124-135 —
+ * never materialised here).  Computes for this block
+ *     eta = X.beta[:d] + beta[d];  mu = link_inv(eta)
+ *     obj  = family objective summed over rows            (stats_d[p*p + p])
+ *     g    = [X,1]^T (mu - y)                              (stats_d[p*p .. p*p+p))
+ *     H    = [X,1]^T diag(w) [X,1], w = mu(1-mu) | 1 | mu  (stats_d[0 .. p*p), row-major)
+ * into ONE packed buffer stats_d of nb_glm_stats_len(d) doubles, so a single all-reduce sums
+ * the row shards.  want_hess == 0 skips H (L-BFGS / gradient passes) and leaves that part of
+ * stats_d untouched.  Penalty terms are not included (they are added once, after the
+ * all-reduce, by nb_glm_newton_update or the host).  Deterministic. */
+int64_t nb_glm_stats_len(int64_t d);
+size_t nb_glm_scratch_bytes(int device, int64_t n, int64_t d, int want_hess);
+int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx,
+                 const void* y_d, int ydt, const double* beta_d, int want_hess,
+                 double* stats_d, void* scratch_d, size_t scratch_bytes, void* stream);
+
+/* The Newton update of glms.py:660-676 on the (all-reduced) packed stats:
+ *     g += l2vec * beta;  H += diag(l2vec)           (grad_penalty/hessian_penalty :254-272)
+ *     beta_out = beta - inv(H) @ g                    (explicit inverse, linalg.py:246-261)
+ *     gmax_d[0] = max |g|                             (convergence test :674)
+ * l2vec_d may be NULL (no penalty).  info_d as in nb_inv_f64.  scratch: nb_inv_scratch_bytes(p)
+ * + 2*p*p*sizeof(double). */
+size_t nb_glm_newton_scratch_bytes(int64_t p);
+int nb_glm_newton_update(int device, int64_t p, double* stats_d, const double* l2vec_d,
+                         const double* beta_d, double* beta_out_d, double* gmax_d,
+                         int32_t* info_d, void* scratch_d, size_t scratch_bytes, void* stream);
+
+/* mu = link_inv(X.beta[:d] + beta[d]) for predict / forward (glms.py:194-197). */
+int nb_glm_predict(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx,
+                   const double* beta_d, double* mu_d, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NUMS_B200_H */
