@@ -1,0 +1,514 @@
+// The GLM inner loop of nums/models/glms.py (newton :660-676, LBFGS lbfgs.py:102-155) as device
+// passes over one row block of X.
+//
+// Reference per row block and Newton iteration: ~19 NumPy calls, 5 reads + 1 write
+// of X-sized data (X@beta, X^T r, s*X materialised, X^T(sX)).  Here:
+//   d <= 7   one fused pass (k_glm_small): eta, link, objective, gradient and the full Hessian are
+//            accumulated in registers per thread; X and y are read exactly once.
+//   d >= 8   pass 1 (k_glm_rows, HBM-bound): eta, link, objective, g = [X,1]^T r, u = [X,1]^T w and the
+//            weights w[n] (scratch);  pass 2 (gemm_f64, FP64 DMMA, compute-bound for d >~ 40):
+//            G = X^T diag(w) X without materialising w*X.  H = [[G, u], [u^T, sum w]].
+// The intercept column of GLM.fit (glms.py:124-135) is implicit: it is never stored.
+// All cross-thread sums are fixed-order (per-CTA partials in scratch, then an ordered second stage).
+#include "gemm.cuh"
+
+namespace nb {
+
+struct LinkOut { double resid, wgt, obj; };
+
+template <int FAMILY>
+__device__ __forceinline__ LinkOut glm_link(double eta, double y) {
+  LinkOut o;
+  if constexpr (FAMILY == NB_GLM_LOGISTIC) {
+    // glms.py:457-458 link_inv, :470 objective, :485 gradient residual, :495 hessian weights
+    double mu = 1.0 / (1.0 + exp(-eta));
+    o.resid = mu - y;
+    o.wgt = mu * (1.0 - mu);
+    o.obj = -(y * log(mu) + (1.0 - y) * log(1.0 - mu));
+  } else if constexpr (FAMILY == NB_GLM_POISSON) {
+    // glms.py:516-517, :531, :544, :548
+    double mu = exp(eta);
+    o.resid = mu - y;
+    o.wgt = mu;
+    o.obj = mu - y * eta;
+  } else {
+    // glms.py:283-284, :296, :311, :318
+    o.resid = eta - y;
+    o.wgt = 1.0;
+    double e = y - eta;
+    o.obj = e * e;
+  }
+  return o;
+}
+
+template <int FAMILY>
+__device__ __forceinline__ double glm_mu(double eta) {
+  if constexpr (FAMILY == NB_GLM_LOGISTIC) return 1.0 / (1.0 + exp(-eta));
+  else if constexpr (FAMILY == NB_GLM_POISSON) return exp(eta);
+  else return eta;
+}
+
+__device__ __forceinline__ double load_y(const void* y, int ydt, int64_t i) {
+  return ydt == NB_F64 ? ((const double*)y)[i] : (double)((const int64_t*)y)[i];
+}
+
+constexpr int GLM_THREADS = 256;
+
+// ------------------------------------------------------------------------------------------------
+// d <= 7: fully fused, one thread per row, everything in registers.
+// Per-CTA partial layout: [H upper triangle row-major: P*(P+1)/2][g: P][obj: 1]
+// ------------------------------------------------------------------------------------------------
+template <int FAMILY, int D>
+__global__ void __launch_bounds__(GLM_THREADS)
+k_glm_small(const double* __restrict__ x, int64_t n, int64_t ldx, const void* __restrict__ y, int ydt,
+            const double* __restrict__ beta, int want_hess, double* __restrict__ partials) {
+  constexpr int P = D + 1;
+  constexpr int NH = P * (P + 1) / 2;
+  constexpr int NV = NH + P + 1;
+  double b[P];
+#pragma unroll
+  for (int j = 0; j < P; j++) b[j] = beta[j];
+  double acc[NV];
+#pragma unroll
+  for (int j = 0; j < NV; j++) acc[j] = 0.0;
+
+  const int64_t stride = (int64_t)gridDim.x * GLM_THREADS;
+  for (int64_t r = (int64_t)blockIdx.x * GLM_THREADS + threadIdx.x; r < n; r += stride) {
+    double xv[P];
+    if constexpr (D == 2) {
+      if ((ldx & 1) == 0 && (((uintptr_t)x) & 15) == 0) {
+        double2 v = *reinterpret_cast<const double2*>(x + r * ldx);
+        xv[0] = v.x; xv[1] = v.y;
+      } else {
+        xv[0] = x[r * ldx]; xv[1] = x[r * ldx + 1];
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < D; j++) xv[j] = x[r * ldx + j];
+    }
+    xv[D] = 1.0;
+    double yv = load_y(y, ydt, r);
+    double eta = b[D];
+#pragma unroll
+    for (int j = 0; j < D; j++) eta = fma(xv[j], b[j], eta);
+    LinkOut lo = glm_link<FAMILY>(eta, yv);
+    acc[NH + P] += lo.obj;
+#pragma unroll
+    for (int j = 0; j < P; j++) acc[NH + j] = fma(lo.resid, xv[j], acc[NH + j]);
+    if (want_hess) {
+      int q = 0;
+#pragma unroll
+      for (int i = 0; i < P; i++) {
+        double wi = lo.wgt * xv[i];
+#pragma unroll
+        for (int j = i; j < P; j++) { acc[q] = fma(wi, xv[j], acc[q]); q++; }
+      }
+    }
+  }
+  // block reduction, fixed order: lanes (tree), then warps
+  __shared__ double sm[GLM_THREADS / 32][NV];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < NV; j++) {
+    double v = acc[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) sm[warp][j] = v;
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < NV; j += GLM_THREADS) {
+    double s = sm[0][j];
+    for (int w = 1; w < GLM_THREADS / 32; w++) s += sm[w][j];
+    partials[(size_t)blockIdx.x * NV + j] = s;
+  }
+}
+
+// Second stage for k_glm_small: sums CTA partials in order and unpacks into the stats buffer.
+__global__ void __launch_bounds__(64)
+k_glm_small_finish(int P, int nparts, const double* __restrict__ partials, int want_hess, double* __restrict__ stats) {
+  const int NH = P * (P + 1) / 2;
+  const int NV = NH + P + 1;
+  __shared__ double tot[64];
+  for (int j = threadIdx.x; j < NV; j += 64) {
+    double s = 0.0;
+    for (int c = 0; c < nparts; c++) s += partials[(size_t)c * NV + j];
+    tot[j] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (want_hess) {
+      int q = 0;
+      for (int i = 0; i < P; i++)
+        for (int j = i; j < P; j++) { stats[i * P + j] = tot[q]; stats[j * P + i] = tot[q]; q++; }
+    }
+    for (int j = 0; j < P; j++) stats[P * P + j] = tot[NH + j];
+    stats[P * P + P] = tot[NH + P];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// d >= 8, pass 1: eta / link / objective / g / u / weights.  HBM-bound: X is read once, straight
+// into registers with 16-byte loads; each warp owns R rows x (64*NJ) columns per step.
+// WPR warps share one row when d > 1024 (partial dot products meet in shared memory).
+// ------------------------------------------------------------------------------------------------
+struct GlmRowsArgs {
+  const double* x; int64_t n, d, ldx;
+  const void* y; int ydt;
+  const double* beta;
+  int family, want_hess;
+  double* wbuf;        // n weights for pass 2 (null: not needed)
+  double* partials;    // [gridDim.x][2*d + 3]
+};
+
+__device__ __forceinline__ LinkOut glm_link_rt(int family, double eta, double y) {
+  if (family == NB_GLM_LOGISTIC) return glm_link<NB_GLM_LOGISTIC>(eta, y);
+  if (family == NB_GLM_POISSON) return glm_link<NB_GLM_POISSON>(eta, y);
+  return glm_link<NB_GLM_LINEAR>(eta, y);
+}
+
+template <int NJ, int WPR, bool VEC>
+__global__ void __launch_bounds__(GLM_THREADS)
+k_glm_rows(const GlmRowsArgs a) {
+  constexpr int R = NJ <= 4 ? 4 : (NJ == 8 ? 2 : 1);
+  constexpr int NE = 2 * NJ;
+  constexpr int NW = GLM_THREADS / 32;
+  constexpr int RG = NW / WPR;
+  constexpr int CW = 64 * NJ;
+  extern __shared__ __align__(16) double dyn[];
+  double* s_beta = dyn;                         // d + 1
+  double* s_acc = dyn + ((a.d + 2) & ~(int64_t)1);  // 2 * WPR * CW  (g then u), then 4 scalars
+  __shared__ double s_eta[2][RG][WPR][R];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rg = warp / WPR, wc = warp % WPR;
+  const int64_t d = a.d, n = a.n;
+  for (int64_t j = tid; j <= d; j += GLM_THREADS) s_beta[j] = a.beta[j];
+  for (int j = tid; j < 2 * WPR * CW + 4; j += GLM_THREADS) s_acc[j] = 0.0;
+  __syncthreads();
+
+  // column owned by this lane for element slot e (compile-time e): cheap to recompute, so not kept in registers
+  const int c0 = wc * CW + (VEC ? 2 * lane : lane);
+#define COL(e) (c0 + (VEC ? (64 * ((e) >> 1) + ((e) & 1)) : 32 * (e)))
+#define CV(e) ((int64_t)COL(e) < d)
+  double bet[NJ <= 4 ? NE : 1];
+  if constexpr (NJ <= 4) {
+#pragma unroll
+    for (int e = 0; e < NE; e++) bet[e] = CV(e) ? s_beta[COL(e)] : 0.0;
+  }
+  const double beta0 = s_beta[d];
+
+  double g[NE], u[NE];
+#pragma unroll
+  for (int e = 0; e < NE; e++) { g[e] = 0.0; u[e] = 0.0; }
+  double gi = 0.0, ui = 0.0, ob = 0.0;
+
+  const int64_t nbatches = (n + R - 1) / R;
+  const int64_t per_it = (int64_t)gridDim.x * RG;
+  const int64_t iters = (nbatches + per_it - 1) / per_it;
+  int buf = 0;
+  for (int64_t it = 0; it < iters; it++) {
+    const int64_t batch = it * per_it + (int64_t)blockIdx.x * RG + rg;
+    const int64_t row0 = batch * R;
+    double xv[R][NE];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int64_t row = row0 + r;
+      const double* xr = a.x + row * a.ldx;
+      if constexpr (VEC) {
+#pragma unroll
+        for (int j = 0; j < NJ; j++) {
+          double2 v = make_double2(0.0, 0.0);
+          if (row < n && CV(2 * j)) {
+            if (CV(2 * j + 1)) v = *reinterpret_cast<const double2*>(xr + COL(2 * j));
+            else v.x = xr[COL(2 * j)];
+          }
+          xv[r][2 * j] = v.x; xv[r][2 * j + 1] = v.y;
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < NE; e++) xv[r][e] = (row < n && CV(e)) ? xr[COL(e)] : 0.0;
+      }
+    }
+    double part[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      double s = 0.0;
+#pragma unroll
+      for (int e = 0; e < NE; e++) {
+        double bv;
+        if constexpr (NJ <= 4) bv = bet[e];
+        else bv = CV(e) ? s_beta[COL(e)] : 0.0;
+        s = fma(xv[r][e], bv, s);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      part[r] = s;
+    }
+    if constexpr (WPR > 1) {
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < R; r++) s_eta[buf][rg][wc][r] = part[r];
+      }
+      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < WPR; w++) s += s_eta[buf][rg][w][r];
+        part[r] = s;
+      }
+      buf ^= 1;
+    }
+    // lane l < R evaluates the link for row l of the batch (other lanes mirror lane l % R)
+    double eta = part[0];
+#pragma unroll
+    for (int r = 1; r < R; r++) if ((lane % R) == r) eta = part[r];
+    eta += beta0;
+    const int64_t myrow = row0 + (lane % R);
+    const bool inb = myrow < n;
+    LinkOut lo = glm_link_rt(a.family, eta, inb ? load_y(a.y, a.ydt, myrow) : 0.0);
+    if (!inb) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
+    if (wc == 0 && lane < R && inb) {
+      ob += lo.obj; gi += lo.resid; ui += lo.wgt;
+      if (a.wbuf) a.wbuf[myrow] = lo.wgt;
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const double rr = __shfl_sync(0xffffffffu, lo.resid, r);
+#pragma unroll
+      for (int e = 0; e < NE; e++) g[e] = fma(rr, xv[r][e], g[e]);
+      if (a.want_hess) {
+        const double ww = __shfl_sync(0xffffffffu, lo.wgt, r);
+#pragma unroll
+        for (int e = 0; e < NE; e++) u[e] = fma(ww, xv[r][e], u[e]);
+      }
+    }
+  }
+
+  // CTA reduction over the row groups, in row-group order (deterministic)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    gi += __shfl_down_sync(0xffffffffu, gi, o);
+    ui += __shfl_down_sync(0xffffffffu, ui, o);
+    ob += __shfl_down_sync(0xffffffffu, ob, o);
+  }
+  double* s_g = s_acc;
+  double* s_u = s_acc + WPR * CW;
+  double* s_sc = s_acc + 2 * WPR * CW;
+  for (int q = 0; q < RG; q++) {
+    if (rg == q) {
+#pragma unroll
+      for (int e = 0; e < NE; e++) {
+        if (CV(e)) { s_g[COL(e)] += g[e]; s_u[COL(e)] += u[e]; }
+      }
+      if (wc == 0 && lane == 0) { s_sc[0] += gi; s_sc[1] += ui; s_sc[2] += ob; }
+    }
+    __syncthreads();
+  }
+  double* out = a.partials + (size_t)blockIdx.x * (2 * d + 3);
+  for (int64_t j = tid; j < d; j += GLM_THREADS) { out[j] = s_g[j]; out[d + j] = s_u[j]; }
+  if (tid == 0) { out[2 * d] = s_sc[0]; out[2 * d + 1] = s_sc[1]; out[2 * d + 2] = s_sc[2]; }
+}
+
+#undef COL
+#undef CV
+
+// Sums the CTA partials (in CTA order) and writes g, obj and the intercept row/column of H.
+__global__ void __launch_bounds__(256)
+k_glm_rows_finish(int64_t d, int nparts, const double* __restrict__ partials, int want_hess,
+                  double* __restrict__ stats) {
+  const int64_t p = d + 1, ps = 2 * d + 3;
+  for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < ps; j += (int64_t)gridDim.x * 256) {
+    double s = 0.0;
+    for (int c = 0; c < nparts; c++) s += partials[(size_t)c * ps + j];
+    if (j < d) {
+      stats[p * p + j] = s;                               // g[j]
+    } else if (j < 2 * d) {
+      if (want_hess) { int64_t i = j - d; stats[i * p + d] = s; stats[d * p + i] = s; }   // u
+    } else if (j == 2 * d) {
+      stats[p * p + d] = s;                               // g[intercept] = sum r
+    } else if (j == 2 * d + 1) {
+      if (want_hess) stats[d * p + d] = s;                // sum w
+    } else {
+      stats[p * p + p] = s;                               // objective
+    }
+  }
+}
+
+// mu = link_inv(X beta + beta0), one warp per row
+__global__ void __launch_bounds__(GLM_THREADS)
+k_glm_predict(int family, const double* __restrict__ x, int64_t n, int64_t d, int64_t ldx,
+              const double* __restrict__ beta, double* __restrict__ mu) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (int64_t)gridDim.x * (GLM_THREADS / 32);
+  const double b0 = beta[d];
+  for (int64_t r = (int64_t)blockIdx.x * (GLM_THREADS / 32) + (threadIdx.x >> 5); r < n; r += warps) {
+    const double* row = x + r * ldx;
+    double s = 0.0;
+    for (int64_t j = lane; j < d; j += 32) s = fma(row[j], beta[j], s);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+      double eta = s + b0;
+      mu[r] = family == NB_GLM_LOGISTIC ? glm_mu<NB_GLM_LOGISTIC>(eta)
+            : (family == NB_GLM_POISSON ? glm_mu<NB_GLM_POISSON>(eta) : eta);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+struct GlmLayout {
+  size_t off_w, off_parts, off_gemm, total;
+  int max_parts;
+};
+
+static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
+  GlmLayout L;
+  const int sms = dev_info(device).sms;
+  L.max_parts = sms * 4;
+  size_t cur = 0;
+  L.off_w = cur;
+  if (want_hess && d >= 8) cur += align256((size_t)n * sizeof(double));
+  L.off_parts = cur;
+  size_t per = d >= 8 ? (size_t)(2 * d + 3) : 64;
+  cur += align256((size_t)L.max_parts * per * sizeof(double));
+  L.off_gemm = cur;
+  if (want_hess && d >= 8) cur += align256(gemm_scratch_bytes(device, d, d, n));
+  L.total = cur;
+  return L;
+}
+
+template <int FAMILY, int D>
+static int launch_small(int device, const double* x, int64_t n, int64_t ldx, const void* y, int ydt,
+                        const double* beta, int want_hess, double* stats, double* parts, int max_parts,
+                        cudaStream_t st) {
+  int64_t blocks = (n + GLM_THREADS * 2 - 1) / (GLM_THREADS * 2);
+  if (blocks > max_parts) blocks = max_parts;
+  if (blocks < 1) blocks = 1;
+  k_glm_small<FAMILY, D><<<(unsigned)blocks, GLM_THREADS, 0, st>>>(x, n, ldx, y, ydt, beta, want_hess, parts);
+  NB_LAUNCH_CHECK();
+  k_glm_small_finish<<<1, 64, 0, st>>>(D + 1, (int)blocks, parts, want_hess, stats);
+  NB_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int FAMILY>
+static int launch_small_d(int device, int64_t d, const double* x, int64_t n, int64_t ldx, const void* y, int ydt,
+                          const double* beta, int want_hess, double* stats, double* parts, int max_parts,
+                          cudaStream_t st) {
+  switch (d) {
+#define NB_SMALL(DD) case DD: return launch_small<FAMILY, DD>(device, x, n, ldx, y, ydt, beta, want_hess, stats, parts, max_parts, st);
+    NB_SMALL(1) NB_SMALL(2) NB_SMALL(3) NB_SMALL(4) NB_SMALL(5) NB_SMALL(6) NB_SMALL(7)
+#undef NB_SMALL
+  }
+  set_error("glm small path: d=%lld out of range", (long long)d);
+  return 2;
+}
+
+template <int NJ, int WPR, bool VEC>
+static int launch_rows(int device, const GlmRowsArgs& a, int max_parts, int* nparts, cudaStream_t st) {
+  auto kern = k_glm_rows<NJ, WPR, VEC>;
+  size_t smem = ((size_t)((a.d + 2) & ~(int64_t)1) + 2 * (size_t)WPR * 64 * NJ + 4) * sizeof(double);
+  NB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, GLM_THREADS, smem));
+  if (occ < 1) occ = 1;
+  constexpr int R = NJ <= 4 ? 4 : (NJ == 8 ? 2 : 1);
+  constexpr int RG = (GLM_THREADS / 32) / WPR;
+  int64_t batches = (a.n + R - 1) / R;
+  int64_t want = (batches + RG - 1) / RG;
+  int64_t grid = (int64_t)dev_info(device).sms * occ;
+  if (grid > max_parts) grid = max_parts;
+  if (grid > want) grid = want;
+  if (grid < 1) grid = 1;
+  kern<<<(unsigned)grid, GLM_THREADS, smem, st>>>(a);
+  NB_LAUNCH_CHECK();
+  *nparts = (int)grid;
+  return 0;
+}
+
+template <bool VEC>
+static int launch_rows_cfg(int device, const GlmRowsArgs& a, int max_parts, int* nparts, cudaStream_t st) {
+  const int64_t d = a.d;
+  if (d <= 64) return launch_rows<1, 1, VEC>(device, a, max_parts, nparts, st);
+  if (d <= 128) return launch_rows<2, 1, VEC>(device, a, max_parts, nparts, st);
+  if (d <= 256) return launch_rows<4, 1, VEC>(device, a, max_parts, nparts, st);
+  if (d <= 512) return launch_rows<8, 1, VEC>(device, a, max_parts, nparts, st);
+  if (d <= 1024) return launch_rows<16, 1, VEC>(device, a, max_parts, nparts, st);
+  if (d <= 2048) return launch_rows<16, 2, VEC>(device, a, max_parts, nparts, st);
+  if (d <= 4096) return launch_rows<16, 4, VEC>(device, a, max_parts, nparts, st);
+  if (d <= 8192) return launch_rows<16, 8, VEC>(device, a, max_parts, nparts, st);
+  set_error("nb_glm_stats: d=%lld > 8192 is not supported", (long long)d);
+  return 2;
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+int64_t nb_glm_stats_len(int64_t d) { int64_t p = d + 1; return p * p + p + 1; }
+
+size_t nb_glm_scratch_bytes(int device, int64_t n, int64_t d, int want_hess) {
+  return glm_layout(device, n, d, want_hess).total;
+}
+
+int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx, const void* y_d,
+                 int ydt, const double* beta_d, int want_hess, double* stats_d, void* scratch_d,
+                 size_t scratch_bytes, void* stream) {
+  NB_ENTER(device);
+  NB_REQUIRE(family >= NB_GLM_LINEAR && family <= NB_GLM_POISSON, "nb_glm_stats: unknown family %d", family);
+  NB_REQUIRE(d >= 1 && n >= 0 && ldx >= d, "nb_glm_stats: bad shape n=%lld d=%lld ldx=%lld", (long long)n,
+             (long long)d, (long long)ldx);
+  NB_REQUIRE(ydt == NB_F64 || ydt == NB_I64, "nb_glm_stats: y dtype %d not supported", ydt);
+  GlmLayout L = glm_layout(device, n, d, want_hess);
+  NB_REQUIRE(scratch_d != nullptr && scratch_bytes >= L.total, "nb_glm_stats: scratch too small (%zu < %zu)",
+             scratch_bytes, L.total);
+  char* sc = (char*)scratch_d;
+  double* parts = (double*)(sc + L.off_parts);
+  if (d <= 7) {
+    switch (family) {
+      case NB_GLM_LOGISTIC: return launch_small_d<NB_GLM_LOGISTIC>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
+      case NB_GLM_POISSON: return launch_small_d<NB_GLM_POISSON>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
+      default: return launch_small_d<NB_GLM_LINEAR>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
+    }
+  }
+  GlmRowsArgs a;
+  a.x = x_d; a.n = n; a.d = d; a.ldx = ldx; a.y = y_d; a.ydt = ydt; a.beta = beta_d;
+  a.family = family; a.want_hess = want_hess;
+  const bool need_w = want_hess && family != NB_GLM_LINEAR;
+  a.wbuf = need_w ? (double*)(sc + L.off_w) : nullptr;
+  a.partials = parts;
+  int nparts = 0;
+  const bool vec = ((ldx & 1) == 0) && ((((uintptr_t)x_d) & 15) == 0);
+  int rc = vec ? launch_rows_cfg<true>(device, a, L.max_parts, &nparts, st)
+               : launch_rows_cfg<false>(device, a, L.max_parts, &nparts, st);
+  if (rc) return rc;
+  k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 255) / 256), 256, 0, st>>>(d, nparts, parts, want_hess, stats_d);
+  NB_LAUNCH_CHECK();
+  if (want_hess) {
+    // G = X^T diag(w) X into the top-left d x d of the p x p Hessian (row stride p)
+    rc = gemm_f64(device, d, d, n, x_d, 1, ldx, x_d, ldx, 1, a.wbuf, stats_d, d + 1, sc + L.off_gemm,
+                  L.total - L.off_gemm, st);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+int nb_glm_predict(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx,
+                   const double* beta_d, double* mu_d, void* stream) {
+  NB_ENTER(device);
+  if (n == 0) return 0;
+  int64_t blocks = (n + 7) / 8;
+  int64_t cap = (int64_t)dev_info(device).sms * 8;
+  k_glm_predict<<<(unsigned)(blocks < cap ? blocks : cap), GLM_THREADS, 0, st>>>(family, x_d, n, d, ldx, beta_d, mu_d);
+  NB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

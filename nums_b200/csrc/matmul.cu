@@ -1,0 +1,674 @@
+// FP64 contractions: KernelCls.bop "tensordot" branch (nums/core/kernel/numpy_kernel.py:419-425)
+// and the weighted Gram X^T.diag(w).X of the GLM Hessian (nums/models/glms.py:491-499, 548).
+//
+// Matrix.matrix: FP64 tensor-core tiles.  sm_100a's FP64 tensor instruction is DMMA.8x8x4
+// (mma.sync.aligned.m8n8k4.f64; tcgen05 has no f64 kind), fed from shared memory through a
+// multi-stage cp.async pipeline with padded (stride = 4 mod 16 doubles) tiles so every fragment
+// load is bank-conflict free.  Tall-skinny contractions (huge k, small m,n) are split along k over
+// the whole grid; partial tiles go to caller-provided scratch and are summed in a fixed order
+// (deterministic, no atomics).  Matrix.vector / dot are HBM-bound streaming kernels.
+#include "gemm.cuh"
+
+namespace nb {
+
+// ------------------------------------------------------------------------------------------------
+// PTX helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(s), "l"(gmem), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem, int src_bytes) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" :: "r"(s), "l"(gmem), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N)); }
+
+// ------------------------------------------------------------------------------------------------
+// GEMM
+// ------------------------------------------------------------------------------------------------
+constexpr int GEMM_BK = 16;
+constexpr int GEMM_PAD = 4;
+
+struct GemmArgs {
+  int64_t m, n, k;
+  const double* a; int64_t lda;   // A_MC: element (k,m) at a[k*lda+m];  else (m,k) at a[m*lda+k]
+  const double* b; int64_t ldb;   // B_NC: element (k,n) at b[k*ldb+n];  else (n,k) at b[n*ldb+k]
+  const double* w;                // optional weights along k
+  double* c; int64_t ldc;
+  double* part;                   // [splits][ntiles][BM*BN] when splits > 1
+  int tiles_m, tiles_n, ntiles, splits, sym;
+  int64_t kchunk;                 // k range per split (multiple of GEMM_BK)
+};
+
+template <int BM, int BN, bool A_MC, bool B_NC>
+struct GemmSmem {
+  static constexpr int A_ROWS = A_MC ? GEMM_BK : BM;
+  static constexpr int A_COLS = A_MC ? BM : GEMM_BK;
+  static constexpr int B_ROWS = B_NC ? GEMM_BK : BN;
+  static constexpr int B_COLS = B_NC ? BN : GEMM_BK;
+  static constexpr int A_LD = A_COLS + GEMM_PAD;
+  static constexpr int B_LD = B_COLS + GEMM_PAD;
+  static constexpr int A_ELEMS = A_ROWS * A_LD;
+  static constexpr int B_ELEMS = B_ROWS * B_LD;
+  static constexpr int STAGE_ELEMS = A_ELEMS + B_ELEMS + GEMM_BK;   // + weights
+};
+
+// Copies a ROWS x COLS tile (COLS contiguous in global memory) into padded shared memory,
+// zero-filling everything outside [row_lim, col_lim).
+template <int ROWS, int COLS, int LD, int NT, bool AL>
+__device__ __forceinline__ void load_tile(double* sm, const double* __restrict__ g, int64_t ld, int64_t row0,
+                                          int64_t col0, int64_t row_lim, int64_t col_lim, int tid) {
+  if constexpr (AL) {
+    constexpr int CPR = COLS / 2;  // 16-byte chunks per row
+    constexpr int TOTAL = ROWS * CPR;
+#pragma unroll
+    for (int c = tid; c < TOTAL; c += NT) {
+      int r = c / CPR, cc = (c % CPR) * 2;
+      int64_t gr = row0 + r, gc = col0 + cc;
+      int bytes = 0;
+      if (gr < row_lim) {
+        int64_t rem = col_lim - gc;
+        bytes = rem >= 2 ? 16 : (rem == 1 ? 8 : 0);
+      }
+      const double* src = bytes ? g + gr * ld + gc : g;
+      cp_async16(sm + r * LD + cc, src, bytes);
+    }
+  } else {
+    constexpr int TOTAL = ROWS * COLS;
+#pragma unroll 4
+    for (int c = tid; c < TOTAL; c += NT) {
+      int r = c / COLS, cc = c % COLS;
+      int64_t gr = row0 + r, gc = col0 + cc;
+      int bytes = (gr < row_lim && gc < col_lim) ? 8 : 0;
+      const double* src = bytes ? g + gr * ld + gc : g;
+      cp_async8(sm + r * LD + cc, src, bytes);
+    }
+  }
+}
+
+template <int BM, int BN, int WM, int WN, int WK, int STAGES, bool A_MC, bool B_NC, bool AL>
+__global__ void __launch_bounds__((BM / WM) * (BN / WN) * WK * 32)
+k_gemm(const GemmArgs g) {
+  using SM = GemmSmem<BM, BN, A_MC, B_NC>;
+  constexpr int WARPS_M = BM / WM, WARPS_N = BN / WN;
+  constexpr int NT = WARPS_M * WARPS_N * WK * 32;
+  constexpr int FM = WM / 8, FN = WN / 8;
+  constexpr int KSTEPS = GEMM_BK / 4;
+  static_assert(KSTEPS % WK == 0, "k-split must divide the k steps of a stage");
+  extern __shared__ __align__(16) double smem[];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int wk = warp / (WARPS_M * WARPS_N);
+  const int wmn = warp % (WARPS_M * WARPS_N);
+  const int wm = wmn / WARPS_N, wn = wmn % WARPS_N;
+  const int lq = lane >> 2, lr = lane & 3;   // groupID, threadID_in_group
+
+  // which tile / split
+  const int t = blockIdx.x % g.ntiles;
+  const int z = blockIdx.x / g.ntiles;
+  int tm, tn;
+  if (g.sym) {          // upper-triangular tile list, row by row
+    int rem = t; tm = 0;
+    while (rem >= g.tiles_n - tm) { rem -= g.tiles_n - tm; tm++; }
+    tn = tm + rem;
+  } else {
+    tm = t / g.tiles_n; tn = t % g.tiles_n;
+  }
+  const int64_t m0 = (int64_t)tm * BM, n0 = (int64_t)tn * BN;
+  const int64_t kbeg = (int64_t)z * g.kchunk;
+  const int64_t kend = (kbeg + g.kchunk < g.k) ? kbeg + g.kchunk : g.k;
+  const int ktiles = kend > kbeg ? (int)((kend - kbeg + GEMM_BK - 1) / GEMM_BK) : 0;
+
+  auto load_stage = [&](int slot, int kt) {
+    double* sA = smem + (size_t)slot * SM::STAGE_ELEMS;
+    double* sB = sA + SM::A_ELEMS;
+    double* sW = sB + SM::B_ELEMS;
+    const int64_t k0 = kbeg + (int64_t)kt * GEMM_BK;
+    if constexpr (A_MC) load_tile<SM::A_ROWS, SM::A_COLS, SM::A_LD, NT, AL>(sA, g.a, g.lda, k0, m0, kend, g.m, tid);
+    else                load_tile<SM::A_ROWS, SM::A_COLS, SM::A_LD, NT, AL>(sA, g.a, g.lda, m0, k0, g.m, kend, tid);
+    if constexpr (B_NC) load_tile<SM::B_ROWS, SM::B_COLS, SM::B_LD, NT, AL>(sB, g.b, g.ldb, k0, n0, kend, g.n, tid);
+    else                load_tile<SM::B_ROWS, SM::B_COLS, SM::B_LD, NT, AL>(sB, g.b, g.ldb, n0, k0, g.n, kend, tid);
+    if (g.w != nullptr && tid < GEMM_BK) {
+      int64_t kk = k0 + tid;
+      cp_async8(sW + tid, kk < kend ? g.w + kk : g.w, kk < kend ? 8 : 0);
+    }
+  };
+
+  double acc[FM][FN][2];
+#pragma unroll
+  for (int i = 0; i < FM; i++)
+#pragma unroll
+    for (int j = 0; j < FN; j++) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; s++) {
+    if (s < ktiles) load_stage(s, s);
+    cp_async_commit();
+  }
+  const bool has_w = g.w != nullptr;
+  for (int kt = 0; kt < ktiles; kt++) {
+    cp_async_wait<STAGES - 2>();
+    __syncthreads();
+    {
+      int nk = kt + STAGES - 1;
+      if (nk < ktiles) load_stage(nk % STAGES, nk);
+      cp_async_commit();
+    }
+    const double* sA = smem + (size_t)(kt % STAGES) * SM::STAGE_ELEMS;
+    const double* sB = sA + SM::A_ELEMS;
+    const double* sW = sB + SM::B_ELEMS;
+#pragma unroll
+    for (int ks = 0; ks < KSTEPS / WK; ks++) {
+      const int kk = (ks * WK + wk) * 4 + lr;
+      double af[FM], bf[FN];
+#pragma unroll
+      for (int i = 0; i < FM; i++) {
+        int mm = wm * WM + i * 8 + lq;
+        af[i] = A_MC ? sA[kk * SM::A_LD + mm] : sA[mm * SM::A_LD + kk];
+      }
+#pragma unroll
+      for (int j = 0; j < FN; j++) {
+        int nn = wn * WN + j * 8 + lq;
+        bf[j] = B_NC ? sB[kk * SM::B_LD + nn] : sB[nn * SM::B_LD + kk];
+      }
+      if (has_w) {
+        double wv = sW[kk];
+#pragma unroll
+        for (int j = 0; j < FN; j++) bf[j] *= wv;
+      }
+#pragma unroll
+      for (int i = 0; i < FM; i++)
+#pragma unroll
+        for (int j = 0; j < FN; j++) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();
+
+  // intra-CTA k-split: groups wk > 0 hand their accumulators to group 0 through shared memory
+  if constexpr (WK > 1) {
+    constexpr int PER_WARP = FM * FN * 2 * 32;
+    for (int src = 1; src < WK; src++) {
+      if (wk == src) {
+        double* dst = smem + (size_t)wmn * PER_WARP;
+#pragma unroll
+        for (int i = 0; i < FM; i++)
+#pragma unroll
+          for (int j = 0; j < FN; j++) {
+            dst[((i * FN + j) * 2 + 0) * 32 + lane] = acc[i][j][0];
+            dst[((i * FN + j) * 2 + 1) * 32 + lane] = acc[i][j][1];
+          }
+      }
+      __syncthreads();
+      if (wk == 0) {
+        const double* s2 = smem + (size_t)wmn * PER_WARP;
+#pragma unroll
+        for (int i = 0; i < FM; i++)
+#pragma unroll
+          for (int j = 0; j < FN; j++) {
+            acc[i][j][0] += s2[((i * FN + j) * 2 + 0) * 32 + lane];
+            acc[i][j][1] += s2[((i * FN + j) * 2 + 1) * 32 + lane];
+          }
+      }
+      __syncthreads();
+    }
+    if (wk != 0) return;
+  }
+
+  if (g.splits > 1) {
+    double* p = g.part + ((size_t)z * g.ntiles + t) * (size_t)(BM * BN);
+#pragma unroll
+    for (int i = 0; i < FM; i++)
+#pragma unroll
+      for (int j = 0; j < FN; j++) {
+        int r = wm * WM + i * 8 + lq, c = wn * WN + j * 8 + 2 * lr;
+        *reinterpret_cast<double2*>(p + r * BN + c) = make_double2(acc[i][j][0], acc[i][j][1]);
+      }
+  } else {
+#pragma unroll
+    for (int i = 0; i < FM; i++)
+#pragma unroll
+      for (int j = 0; j < FN; j++) {
+        int64_t r = m0 + wm * WM + i * 8 + lq, c = n0 + wn * WN + j * 8 + 2 * lr;
+        if (r < g.m) {
+          if (c < g.n) g.c[r * g.ldc + c] = acc[i][j][0];
+          if (c + 1 < g.n) g.c[r * g.ldc + c + 1] = acc[i][j][1];
+          if (g.sym && tm != tn) {   // mirror the off-diagonal tile
+            if (c < g.n) g.c[c * g.ldc + r] = acc[i][j][0];
+            if (c + 1 < g.n) g.c[(c + 1) * g.ldc + r] = acc[i][j][1];
+          }
+        }
+      }
+  }
+}
+
+// Sums split-k partial tiles in split order and scatters them (with mirroring in sym mode) into C.
+template <int BM, int BN>
+__global__ void __launch_bounds__(256)
+k_gemm_reduce(const GemmArgs g) {
+  const int64_t total = g.m * g.n;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < total; e += stride) {
+    int64_t r = e / g.n, c = e - r * g.n;
+    int tm = (int)(r / BM), tn = (int)(c / BN);
+    int lr_ = (int)(r - (int64_t)tm * BM), lc = (int)(c - (int64_t)tn * BN);
+    int t;
+    if (g.sym) {
+      if (tn < tm) { int x = tm; tm = tn; tn = x; x = lr_; lr_ = lc; lc = x; }
+      // index of (tm, tn) in the row-by-row upper-triangular list
+      t = tm * g.tiles_n - (tm * (tm - 1)) / 2 + (tn - tm);
+    } else {
+      t = tm * g.tiles_n + tn;
+    }
+    const double* p = g.part + (size_t)t * (BM * BN) + lr_ * BN + lc;
+    double s = 0.0;
+    for (int z = 0; z < g.splits; z++) s += p[(size_t)z * g.ntiles * (BM * BN)];
+    g.c[r * g.ldc + c] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// launch plan
+// ------------------------------------------------------------------------------------------------
+struct GemmPlan {
+  int cfg;            // 0: 128x128 tiles, 1: 64x64, 2: 32x32 (4-way in-CTA k split)
+  int bm, bn;
+  int tiles_m, tiles_n, ntiles, splits, sym;
+  int64_t kchunk;
+  size_t scratch;
+};
+
+static GemmPlan plan_gemm(int device, int64_t m, int64_t n, int64_t k, bool sym) {
+  GemmPlan p;
+  int64_t big = m > n ? m : n;
+  p.cfg = big <= 32 ? 2 : (big <= 64 ? 1 : 0);
+  p.bm = p.bn = p.cfg == 0 ? 128 : (p.cfg == 1 ? 64 : 32);
+  p.tiles_m = (int)((m + p.bm - 1) / p.bm);
+  p.tiles_n = (int)((n + p.bn - 1) / p.bn);
+  p.sym = sym ? 1 : 0;
+  p.ntiles = sym ? p.tiles_m * (p.tiles_m + 1) / 2 : p.tiles_m * p.tiles_n;
+  const int sms = dev_info(device).sms;
+  const int64_t target = (int64_t)sms * (p.cfg == 0 ? 1 : (p.cfg == 1 ? 3 : 4));
+  int64_t splits = target / p.ntiles;
+  int64_t max_splits = (k + GEMM_BK * 8 - 1) / (GEMM_BK * 8);
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  int64_t kchunk = (k + splits - 1) / splits;
+  kchunk = (kchunk + GEMM_BK - 1) / GEMM_BK * GEMM_BK;
+  if (kchunk < GEMM_BK) kchunk = GEMM_BK;
+  splits = (k + kchunk - 1) / kchunk;
+  if (splits < 1) splits = 1;
+  p.splits = (int)splits;
+  p.kchunk = kchunk;
+  p.scratch = splits > 1 ? (size_t)splits * p.ntiles * p.bm * p.bn * sizeof(double) : 0;
+  return p;
+}
+
+template <int BM, int BN, int WM, int WN, int WK, int STAGES, bool A_MC, bool B_NC, bool AL>
+static int launch_gemm(const GemmArgs& g, cudaStream_t st) {
+  using SM = GemmSmem<BM, BN, A_MC, B_NC>;
+  constexpr int NT = (BM / WM) * (BN / WN) * WK * 32;
+  size_t smem = (size_t)STAGES * SM::STAGE_ELEMS * sizeof(double);
+  auto kern = k_gemm<BM, BN, WM, WN, WK, STAGES, A_MC, B_NC, AL>;
+  NB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)(g.ntiles * g.splits), NT, smem, st>>>(g);
+  NB_LAUNCH_CHECK();
+  if (g.splits > 1) {
+    int64_t total = g.m * g.n;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_gemm_reduce<BM, BN><<<(unsigned)blocks, 256, 0, st>>>(g);
+    NB_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+template <bool A_MC, bool B_NC, bool AL>
+static int launch_gemm_cfg(int cfg, const GemmArgs& g, cudaStream_t st) {
+  switch (cfg) {
+    case 0: return launch_gemm<128, 128, 64, 32, 1, 4, A_MC, B_NC, AL>(g, st);
+    case 1: return launch_gemm<64, 64, 32, 32, 1, 4, A_MC, B_NC, AL>(g, st);
+    default: return launch_gemm<32, 32, 32, 32, 4, 4, A_MC, B_NC, AL>(g, st);
+  }
+}
+
+template <bool A_MC, bool B_NC>
+static int launch_gemm_al(bool al, int cfg, const GemmArgs& g, cudaStream_t st) {
+  return al ? launch_gemm_cfg<A_MC, B_NC, true>(cfg, g, st) : launch_gemm_cfg<A_MC, B_NC, false>(cfg, g, st);
+}
+
+// ------------------------------------------------------------------------------------------------
+// matrix.vector / dot (HBM-bound)
+// ------------------------------------------------------------------------------------------------
+constexpr int GV_THREADS = 256;
+constexpr int64_t GV_TARGET_BLOCKS = 592;
+
+// y[r*ys] = sum_k A[r*lda + k] * w[k] * x[k*xs], one warp per row (short rows, many of them)
+__global__ void __launch_bounds__(GV_THREADS)
+k_gemv_rows_warp(int64_t m, int64_t k, const double* __restrict__ a, int64_t lda, const double* __restrict__ x,
+                 int64_t xs, const double* __restrict__ w, double* __restrict__ y, int64_t ys) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (int64_t)gridDim.x * (GV_THREADS / 32);
+  for (int64_t r = (int64_t)blockIdx.x * (GV_THREADS / 32) + (threadIdx.x >> 5); r < m; r += warps) {
+    const double* row = a + r * lda;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    int64_t i = lane;
+    for (; i + 96 < k; i += 128) {
+      double v[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) v[u] = row[i + 32 * u];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        double xv = x[(i + 32 * u) * xs];
+        if (w) xv *= w[i + 32 * u];
+        acc[u] = fma(v[u], xv, acc[u]);
+      }
+    }
+    for (; i < k; i += 32) {
+      double xv = x[i * xs];
+      if (w) xv *= w[i];
+      acc[0] = fma(row[i], xv, acc[0]);
+    }
+    double s = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if (lane == 0) y[r * ys] = s;
+  }
+}
+
+// part[r*S + s] = sum over the s-th k-chunk of A[r*lda + k] * w[k] * x[k*xs]  (few, long rows; dot)
+__global__ void __launch_bounds__(GV_THREADS)
+k_gemv_rows_split(int64_t m, int64_t k, int64_t S, int64_t chunk, const double* __restrict__ a, int64_t lda,
+                  const double* __restrict__ x, int64_t xs, const double* __restrict__ w, double* __restrict__ part) {
+  __shared__ double sm[8];
+  const int64_t s = blockIdx.x;
+  for (int64_t r = blockIdx.y; r < m; r += gridDim.y) {
+    const int64_t lo = s * chunk, hi = (lo + chunk < k) ? lo + chunk : k;
+    const double* row = a + r * lda;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    int64_t i = lo + threadIdx.x;
+    for (; i + 3 * GV_THREADS < hi; i += 4 * GV_THREADS) {
+      double v[4], xv[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) { v[u] = row[i + u * GV_THREADS]; xv[u] = x[(i + u * GV_THREADS) * xs]; }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        if (w) xv[u] *= w[i + u * GV_THREADS];
+        acc[u] = fma(v[u], xv[u], acc[u]);
+      }
+    }
+    for (; i < hi; i += GV_THREADS) {
+      double xv = x[i * xs];
+      if (w) xv *= w[i];
+      acc[0] = fma(row[i], xv, acc[0]);
+    }
+    double v = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = sm[0];
+      for (int q = 1; q < GV_THREADS / 32; q++) t += sm[q];
+      part[r * S + s] = t;
+    }
+  }
+}
+
+// part[s*m + c] = sum over the s-th k-chunk of A[k*lda + c] * w[k] * x[k*xs]   (X^T v, tall-skinny)
+__global__ void __launch_bounds__(GV_THREADS)
+k_gemv_cols(int64_t m, int64_t k, int64_t chunk, int tile, const double* __restrict__ a, int64_t lda,
+            const double* __restrict__ x, int64_t xs, const double* __restrict__ w, double* __restrict__ part) {
+  __shared__ double sm[GV_THREADS];
+  const int kpar = GV_THREADS / tile;
+  const int t = threadIdx.x;
+  const bool active = t < kpar * tile;
+  const int ti = t % tile, tk = t / tile;
+  const int64_t col = (int64_t)blockIdx.x * tile + ti;
+  const int64_t s = blockIdx.y;
+  const int64_t lo = s * chunk, hi = (lo + chunk < k) ? lo + chunk : k;
+  double acc0 = 0.0, acc1 = 0.0;
+  if (active && col < m) {
+    int64_t kk = lo + tk;
+    for (; kk + kpar < hi; kk += 2 * kpar) {
+      double v0 = a[kk * lda + col], v1 = a[(kk + kpar) * lda + col];
+      double x0 = x[kk * xs], x1 = x[(kk + kpar) * xs];
+      if (w) { x0 *= w[kk]; x1 *= w[kk + kpar]; }
+      acc0 = fma(v0, x0, acc0);
+      acc1 = fma(v1, x1, acc1);
+    }
+    if (kk < hi) {
+      double x0 = x[kk * xs];
+      if (w) x0 *= w[kk];
+      acc0 = fma(a[kk * lda + col], x0, acc0);
+    }
+  }
+  sm[t] = acc0 + acc1;
+  __syncthreads();
+  if (t < tile && col < m) {
+    double r = sm[t];
+    for (int j = 1; j < kpar; j++) r += sm[t + j * tile];
+    part[s * m + col] = r;
+  }
+}
+
+// out[j*os] = sum_s part[s*ss + j*js], in split order
+__global__ void __launch_bounds__(256)
+k_sum_parts(int64_t count, int64_t S, const double* __restrict__ part, int64_t ss, int64_t js,
+            double* __restrict__ out, int64_t os) {
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < count; j += stride) {
+    double s = 0.0;
+    for (int64_t q = 0; q < S; q++) s += part[q * ss + j * js];
+    out[j * os] = s;
+  }
+}
+
+struct GemvPlan { int kind; int64_t S, chunk; int tile; size_t scratch; };
+
+static GemvPlan plan_gemv(int64_t m, int64_t k, bool k_contig) {
+  GemvPlan p;
+  p.tile = 1; p.S = 1; p.chunk = k; p.scratch = 0;
+  if (k_contig) {
+    if (m >= 256 && k <= 16384) { p.kind = 0; return p; }
+    p.kind = 1;
+    int64_t want = GV_TARGET_BLOCKS / (m < GV_TARGET_BLOCKS ? (m > 0 ? m : 1) : GV_TARGET_BLOCKS);
+    if (want < 1) want = 1;
+    int64_t max_s = (k + 4095) / 4096;
+    p.S = want < max_s ? want : max_s;
+  } else {
+    p.kind = 2;
+    p.tile = m >= GV_THREADS ? GV_THREADS : (int)m;
+    int64_t col_blocks = (m + p.tile - 1) / p.tile;
+    int64_t want = col_blocks >= GV_TARGET_BLOCKS ? 1 : GV_TARGET_BLOCKS / col_blocks;
+    int64_t kpar = GV_THREADS / p.tile;
+    int64_t max_s = (k + 16 * kpar - 1) / (16 * kpar);
+    p.S = want < max_s ? want : max_s;
+  }
+  if (p.S < 1) p.S = 1;
+  p.chunk = (k + p.S - 1) / p.S;
+  if (p.chunk < 1) p.chunk = 1;
+  p.S = (k + p.chunk - 1) / p.chunk;
+  if (p.S < 1) p.S = 1;
+  p.scratch = (size_t)p.S * m * sizeof(double);
+  return p;
+}
+
+// y[r*ys] = sum_k A(r,k) * w[k] * x[k*xs];  A(r,k) at a[r*a_rs + k*a_cs], one of a_rs/a_cs == 1.
+static int gemv_f64(int device, int64_t m, int64_t k, const double* a, int64_t a_rs, int64_t a_cs,
+                    const double* x, int64_t xs, const double* w, double* y, int64_t ys, void* scratch,
+                    size_t scratch_bytes, cudaStream_t st) {
+  const bool k_contig = (a_cs == 1) || (m == 1);
+  if (m == 1 && a_cs != 1) { /* single row with stride a_cs: handled as a column walk below */ }
+  if (k_contig && a_cs == 1) {
+    GemvPlan p = plan_gemv(m, k, true);
+    if (p.kind == 0) {
+      int64_t blocks = (m + 7) / 8;
+      int64_t cap = (int64_t)dev_info(device).sms * 8;
+      k_gemv_rows_warp<<<(unsigned)(blocks < cap ? blocks : cap), GV_THREADS, 0, st>>>(m, k, a, a_rs, x, xs, w, y, ys);
+      NB_LAUNCH_CHECK();
+      return 0;
+    }
+    NB_REQUIRE(scratch != nullptr && scratch_bytes >= p.scratch, "matmul: scratch too small (%zu < %zu)",
+               scratch_bytes, p.scratch);
+    dim3 grid((unsigned)p.S, (unsigned)(m < 65535 ? m : 65535));
+    k_gemv_rows_split<<<grid, GV_THREADS, 0, st>>>(m, k, p.S, p.chunk, a, a_rs, x, xs, w, (double*)scratch);
+    NB_LAUNCH_CHECK();
+    int64_t blocks = (m + 255) / 256;
+    k_sum_parts<<<(unsigned)(blocks < 1184 ? blocks : 1184), 256, 0, st>>>(m, p.S, (const double*)scratch, 1, p.S, y, ys);
+    NB_LAUNCH_CHECK();
+    return 0;
+  }
+  // m contiguous (a_rs == 1), or a single strided row (m == 1): walk k with stride a_cs
+  int64_t lda = a_cs;
+  GemvPlan p = plan_gemv(m, k, false);
+  NB_REQUIRE(scratch != nullptr && scratch_bytes >= p.scratch, "matmul: scratch too small (%zu < %zu)",
+             scratch_bytes, p.scratch);
+  dim3 grid((unsigned)((m + p.tile - 1) / p.tile), (unsigned)p.S);
+  k_gemv_cols<<<grid, GV_THREADS, 0, st>>>(m, k, p.chunk, p.tile, a, lda, x, xs, w, (double*)scratch);
+  NB_LAUNCH_CHECK();
+  int64_t blocks = (m + 255) / 256;
+  k_sum_parts<<<(unsigned)(blocks < 1184 ? blocks : 1184), 256, 0, st>>>(m, p.S, (const double*)scratch, m, 1, y, ys);
+  NB_LAUNCH_CHECK();
+  return 0;
+}
+
+static size_t gemv_scratch(int64_t m, int64_t k) {
+  size_t a = plan_gemv(m, k, true).scratch, b = plan_gemv(m, k, false).scratch;
+  return a > b ? a : b;
+}
+
+// ------------------------------------------------------------------------------------------------
+// int64 contraction (NumPy has no BLAS path for integers; wrapping arithmetic)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_matmul_i64(int64_t m, int64_t n, int64_t k, const int64_t* __restrict__ a, int64_t a_rs, int64_t a_cs,
+             const int64_t* __restrict__ b, int64_t b_rs, int64_t b_cs, int64_t* __restrict__ c, int64_t ldc) {
+  // one block per output element, strided over k, fixed-order block reduction
+  __shared__ uint64_t sm[8];
+  const int64_t total = m * n;
+  for (int64_t e = blockIdx.x; e < total; e += gridDim.x) {
+    int64_t r = e / n, cc = e - r * n;
+    uint64_t acc = 0;
+    for (int64_t i = threadIdx.x; i < k; i += 256)
+      acc += (uint64_t)a[r * a_rs + i * a_cs] * (uint64_t)b[i * b_rs + cc * b_cs];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint64_t t = 0;
+      for (int q = 0; q < 8; q++) t += sm[q];
+      c[r * ldc + cc] = (int64_t)t;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_matmul_i64_thread(int64_t m, int64_t n, int64_t k, const int64_t* __restrict__ a, int64_t a_rs, int64_t a_cs,
+                    const int64_t* __restrict__ b, int64_t b_rs, int64_t b_cs, int64_t* __restrict__ c, int64_t ldc) {
+  const int64_t total = m * n;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < total; e += stride) {
+    int64_t r = e / n, cc = e - r * n;
+    uint64_t acc = 0;
+    for (int64_t i = 0; i < k; i++) acc += (uint64_t)a[r * a_rs + i * a_cs] * (uint64_t)b[i * b_rs + cc * b_cs];
+    c[r * ldc + cc] = (int64_t)acc;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// dispatcher
+// ------------------------------------------------------------------------------------------------
+size_t gemm_scratch_bytes(int device, int64_t m, int64_t n, int64_t k) {
+  if (m <= 0 || n <= 0 || k <= 0) return 0;
+  size_t s = 0;
+  if (n == 1) s = gemv_scratch(m, k);
+  else if (m == 1) s = gemv_scratch(n, k);
+  else {
+    size_t a = plan_gemm(device, m, n, k, false).scratch;
+    size_t b = (m == n) ? plan_gemm(device, m, n, k, true).scratch : 0;
+    s = a > b ? a : b;
+  }
+  return s;
+}
+
+int gemm_f64(int device, int64_t m, int64_t n, int64_t k, const double* a, int64_t a_rs, int64_t a_cs,
+             const double* b, int64_t b_rs, int64_t b_cs, const double* w, double* c, int64_t ldc,
+             void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  if (m <= 0 || n <= 0) return 0;
+  if (k <= 0) {  // empty contraction: zeros
+    for (int64_t r = 0; r < m; r++) NB_CHECK(cudaMemsetAsync(c + r * ldc, 0, (size_t)n * sizeof(double), st));
+    return 0;
+  }
+  if (n == 1) return gemv_f64(device, m, k, a, a_rs, a_cs, b, b_rs, w, c, ldc, scratch, scratch_bytes, st);
+  if (m == 1) return gemv_f64(device, n, k, b, b_cs, b_rs, a, a_cs, w, c, 1, scratch, scratch_bytes, st);
+  NB_REQUIRE(a_rs == 1 || a_cs == 1, "matmul: operand A must be contiguous along one axis (strides %lld,%lld)",
+             (long long)a_rs, (long long)a_cs);
+  NB_REQUIRE(b_rs == 1 || b_cs == 1, "matmul: operand B must be contiguous along one axis (strides %lld,%lld)",
+             (long long)b_rs, (long long)b_cs);
+  // a_rs == 1 -> m contiguous (A stored [k][m]); prefer the k-contiguous reading when both are 1
+  const bool a_mc = (a_rs == 1) && (a_cs != 1);
+  const bool b_nc = (b_cs == 1) && (b_rs != 1 || k == 1);
+  GemmArgs g;
+  g.m = m; g.n = n; g.k = k;
+  g.a = a; g.lda = a_mc ? a_cs : a_rs;
+  g.b = b; g.ldb = b_nc ? b_rs : b_cs;
+  g.w = w; g.c = c; g.ldc = ldc;
+  const bool sym = (a == b) && (m == n) && a_mc && b_nc && (a_cs == b_rs);
+  GemmPlan p = plan_gemm(device, m, n, k, sym);
+  g.tiles_m = p.tiles_m; g.tiles_n = p.tiles_n; g.ntiles = p.ntiles; g.splits = p.splits; g.sym = p.sym;
+  g.kchunk = p.kchunk;
+  g.part = (double*)scratch;
+  if (p.splits > 1)
+    NB_REQUIRE(scratch != nullptr && scratch_bytes >= p.scratch, "matmul: scratch too small (%zu < %zu)",
+               scratch_bytes, p.scratch);
+  const bool al = (((uintptr_t)a | (uintptr_t)b) & 15) == 0 && (g.lda % 2 == 0) && (g.ldb % 2 == 0);
+  if (a_mc && b_nc) return launch_gemm_al<true, true>(al, p.cfg, g, st);
+  if (a_mc && !b_nc) return launch_gemm_al<true, false>(al, p.cfg, g, st);
+  if (!a_mc && b_nc) return launch_gemm_al<false, true>(al, p.cfg, g, st);
+  return launch_gemm_al<false, false>(al, p.cfg, g, st);
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+size_t nb_matmul_scratch_bytes(int device, int64_t m, int64_t n, int64_t k) {
+  return gemm_scratch_bytes(device, m, n, k);
+}
+
+int nb_matmul_f64(int device, int64_t m, int64_t n, int64_t k, const double* a_d, int64_t a_rs, int64_t a_cs,
+                  const double* b_d, int64_t b_rs, int64_t b_cs, const double* w_d, double* c_d, int64_t ldc,
+                  void* scratch_d, size_t scratch_bytes, void* stream) {
+  NB_ENTER(device);
+  return gemm_f64(device, m, n, k, a_d, a_rs, a_cs, b_d, b_rs, b_cs, w_d, c_d, ldc, scratch_d, scratch_bytes, st);
+}
+
+int nb_matmul_i64(int device, int64_t m, int64_t n, int64_t k, const int64_t* a_d, int64_t a_rs, int64_t a_cs,
+                  const int64_t* b_d, int64_t b_rs, int64_t b_cs, int64_t* c_d, int64_t ldc, void* stream) {
+  NB_ENTER(device);
+  if (m <= 0 || n <= 0) return 0;
+  int64_t total = m * n;
+  if (total <= 4096 && k >= 1024) {
+    k_matmul_i64<<<(unsigned)total, 256, 0, st>>>(m, n, k, a_d, a_rs, a_cs, b_d, b_rs, b_cs, c_d, ldc);
+  } else {
+    int grid = grid_for(device, total, 256, 1);
+    k_matmul_i64_thread<<<grid, 256, 0, st>>>(m, n, k, a_d, a_rs, a_cs, b_d, b_rs, b_cs, c_d, ldc);
+  }
+  NB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"
