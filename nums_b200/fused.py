@@ -1,0 +1,84 @@
+"""Fused GLM operators, registered with the kernel manager by name (`km.register`, the door the
+reference's own fusion uses: nums/experimental/optimizer/graph.py:801-810, invoked like :957-959).
+
+Each takes/returns DeviceBlocks and calls one C-ABI entry point of libnumsb200.so.
+"""
+import numpy as np
+
+from . import _lib
+from . import device as dv
+from . import hostlogic as hl
+from .device import DeviceBlock
+
+
+def glm_stats(x, y, beta, family, want_hess):
+    """Packed [H (p*p) | g (p) | objective (1)] of one row block (see nb_glm_stats)."""
+    lib = _lib.load()
+    dev = x.device_index
+    if x.ndim != 2 or x.dtype != np.dtype(np.float64):
+        raise TypeError("glm_stats needs a 2-d float64 block, got %s %s" % (x.shape, x.dtype))
+    if x.strides[1] != 1:
+        x = dv.contiguous(x)
+    y = dv.contiguous(y)
+    if y.dtype == np.dtype(np.bool_):
+        raise TypeError("glm_stats: y must be float64 or int64")
+    beta = dv.contiguous(dv.to_device(beta, dev))
+    n, d = x.shape
+    if beta.shape != (d + 1,) or y.shape != (n,):
+        raise ValueError("glm_stats: shapes X%s y%s beta%s do not agree" % (x.shape, y.shape, beta.shape))
+    out = dv.empty((lib.nb_glm_stats_len(d),), np.float64, dev)
+    if not want_hess:   # the H part is not written by the kernel: keep the buffer defined for the all-reduce
+        _lib.check(lib.nb_fill(dev, out.size, out.ptr, out.code, 0.0, 0, dv.stream_ptr(dev)))
+    sc = dv.scratch(lib.nb_glm_scratch_bytes(dev, n, d, int(bool(want_hess))), dev)
+    _lib.check(lib.nb_glm_stats(dev, hl.FAMILY_CODE[family], x.ptr, n, d, x.strides[0], y.ptr, y.code, beta.ptr,
+                                int(bool(want_hess)), out.ptr, sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+    return out
+
+
+def glm_newton_update(stats, l2vec, beta):
+    """(beta - inv(H + diag(l2)) @ (g + l2*beta), max|g + l2*beta|) from packed, already reduced stats.
+    Consumes `stats` (H and g are updated in place with the penalty)."""
+    lib = _lib.load()
+    dev = stats.device_index
+    beta = dv.contiguous(dv.to_device(beta, dev))
+    p = beta.shape[0]
+    if stats.shape != (p * p + p + 1,):
+        raise ValueError("stats length %s does not match p=%d" % (stats.shape, p))
+    l2 = dv.contiguous(dv.to_device(l2vec, dev)) if l2vec is not None else None
+    out = dv.empty((p,), np.float64, dev)
+    gmax = dv.empty((), np.float64, dev)
+    info = dv.empty((1,), np.int32, dev)
+    sc = dv.scratch(lib.nb_glm_newton_scratch_bytes(p), dev)
+    _lib.check(lib.nb_glm_newton_update(dev, p, stats.ptr, l2.ptr if l2 is not None else None, beta.ptr, out.ptr,
+                                        gmax.ptr, info.ptr, sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+    return out, gmax, info
+
+
+def glm_predict(x, beta, family):
+    lib = _lib.load()
+    dev = x.device_index
+    if x.strides[1] != 1:
+        x = dv.contiguous(x)
+    beta = dv.contiguous(dv.to_device(beta, dev))
+    n, d = x.shape
+    out = dv.empty((n,), np.float64, dev)
+    _lib.check(lib.nb_glm_predict(dev, hl.FAMILY_CODE[family], x.ptr, n, d, x.strides[0], beta.ptr, out.ptr,
+                                  dv.stream_ptr(dev)))
+    return out
+
+
+def stats_slice(stats, p, what):
+    """Views into the packed stats block: 'H' (p,p), 'g' (p,), 'obj' ()."""
+    t = stats.t
+    if what == "H":
+        return DeviceBlock(t[: p * p].view(p, p))
+    if what == "g":
+        return DeviceBlock(t[p * p: p * p + p])
+    return DeviceBlock(t[p * p + p])
+
+
+def register(km):
+    km.register("glm_stats", glm_stats, {})
+    km.register("glm_newton_update", glm_newton_update, {})
+    km.register("glm_predict", glm_predict, {})
+    km.register("stats_slice", stats_slice, {})
