@@ -1,0 +1,284 @@
+"""GPU parity tests of the block-array layer and the GLM inner loop against the reference's golden
+vectors and the oracle.  Tolerances are BASELINE.json's: coefficients 1e-8, iteration-0 g / H /
+objective and contractions rel-err 1e-10, indices and integer results bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, rel_err
+from oracle import glm as oglm
+
+pytestmark = pytest.mark.gpu
+COEF_TOL = 1e-8
+STAT_TOL = 1e-10
+
+
+def fit_dev(app, cls, X, y, rb, fused=True, **kw):
+    Xb = app.array(X, block_shape=(rb, X.shape[1]))
+    yb = app.array(y, block_shape=(rb,))
+    m = cls(app=app, fused=fused, **kw)
+    m.fit(Xb, yb)
+    return m, Xb, yb
+
+
+def coef_close(m, beta, beta0, tol=COEF_TOL):
+    got, got0 = m._beta.get(), float(m._beta0.get())
+    scale = max(1.0, float(np.max(np.abs(beta))))
+    assert np.max(np.abs(got - beta)) <= tol * scale, np.max(np.abs(got - beta))
+    assert abs(got0 - float(beta0)) <= tol * max(1.0, abs(float(beta0)))
+
+
+# ------------------------------------------------------------------------------------------------
+# block-array level (BASELINE config 2, scaled to the golden size)
+# ------------------------------------------------------------------------------------------------
+def test_blockarray_dot_where_argmax_sum(app):
+    g = load_golden("blockarray")
+    rb = int(g["row_block"])
+    x = app.array(g["x"], block_shape=(rb,))
+    p = app.array(g["p"], block_shape=(rb,))
+    assert rel_err((x.T @ x).get(), g["dot"]) < STAT_TOL
+    idx = app.where(p == len(g["p"]) // 2)
+    np.testing.assert_array_equal(idx[0].get(), g["where_idx"])
+    assert int(app.sum(p).get()) == int(g["sum_p"])
+    assert int(app.argmax(p).get()) == int(g["argmax_p"])
+    assert int(app.argmin(x).get()) == int(g["argmin_x"])
+    assert float(app.max(x).get()) == float(g["max_x"])
+    assert rel_err(app.mean(x).get(), g["mean_x"]) < STAT_TOL
+
+
+def test_block_rng_matches_reference_stream(app):
+    """app.random draws block j from PCG64(seed).jumped(j): same values as the reference's golden x."""
+    from nums_b200.app import NumsRandomState
+    g = load_golden("blockarray")
+    n = len(g["x"])
+    rs = NumsRandomState(app.km, 1337)
+    x = rs.random(shape=(n,), block_shape=(n // 4,))
+    np.testing.assert_array_equal(x.get(), g["x"])
+    p = rs.permutation(n, n // 4)
+    np.testing.assert_array_equal(p.get(), g["p"])
+
+
+def test_blockarray_elementwise_and_reduce(app):
+    rng = np.random.default_rng(3)
+    A = rng.standard_normal((1000, 12))
+    B = rng.integers(-5, 5, (1000, 12))
+    a, b = app.array(A, block_shape=(300, 12)), app.array(B, block_shape=(300, 12))
+    np.testing.assert_array_equal((a * b + 2.0).get(), A * B + 2.0)
+    np.testing.assert_array_equal((b // 3).get(), B // 3)
+    np.testing.assert_array_equal((b % -4).get(), B % -4)
+    np.testing.assert_array_equal((a > b).get(), A > B)
+    assert rel_err(app.sum(a, axis=0).get(), A.sum(axis=0)) < STAT_TOL
+    assert rel_err(app.sum(a, axis=1).get(), A.sum(axis=1)) < STAT_TOL
+    assert rel_err(app.max(a, axis=0).get(), A.max(axis=0)) == 0.0
+    s = app.sum(b, axis=0)
+    assert s.dtype == np.int64
+    np.testing.assert_array_equal(s.get(), B.sum(axis=0))       # Q1 data is float64, metadata int64
+    col = app.array(A[:, :1].copy(), block_shape=(300, 1))
+    np.testing.assert_array_equal((col * a).get(), A[:, :1] * A)
+    assert rel_err((a.transpose(defer=True) @ a).get(), A.T @ A) < STAT_TOL
+    v = app.array(A[:, 0].copy(), block_shape=(300,))
+    assert rel_err((a.transpose(defer=True) @ v).get(), A.T @ A[:, 0]) < STAT_TOL
+    w = app.where(a > 0, a, -a)
+    np.testing.assert_array_equal(w.get(), np.abs(A))
+
+
+# ------------------------------------------------------------------------------------------------
+# GLM: golden fits
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("fused", [True, False])
+def test_readme_logistic(app, fused):
+    from nums_b200.glms import LogisticRegression
+    g = load_golden("glm_readme")
+    with pytest.warns(UserWarning):
+        m, Xb, _ = fit_dev(app, LogisticRegression, g["X"], g["y"], int(g["row_block"]), fused=fused,
+                           solver="newton-cg", penalty="l2", C=10)
+    coef_close(m, g["beta"], g["beta0"])
+    np.testing.assert_array_equal(m.predict(Xb).get(), g["pred"])
+
+
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("tag,kw", [
+    ("newton_none", dict(solver="newton", penalty="none", max_iter=4)),
+    ("newton_l2", dict(solver="newton", penalty="l2", C=2.0, max_iter=6)),
+    ("lbfgs_l2", dict(solver="lbfgs", penalty="l2", C=2.0, max_iter=6)),
+    ("gd_l2", dict(solver="gd", penalty="l2", C=2.0, max_iter=5, lr=1e-4)),
+])
+def test_logistic_d32(app, fused, tag, kw):
+    from nums_b200.glms import LogisticRegression
+    g = load_golden("glm_logistic_d32")
+    m, _, _ = fit_dev(app, LogisticRegression, g["X"], g["y"], int(g["row_block"]), fused=fused, **kw)
+    coef_close(m, g[tag + "_beta"], g[tag + "_beta0"])
+
+
+def test_logistic_iteration0_stats_d32(app):
+    """g, H, objective at a fixed beta against the reference's own model methods."""
+    from nums_b200.glms import LogisticRegression
+    g = load_golden("glm_logistic_d32")
+    rb, d = int(g["row_block"]), g["X"].shape[1]
+    Xb = app.array(g["X"], block_shape=(rb, d))
+    yb = app.array(g["y"], block_shape=(rb,))
+    m = LogisticRegression(app=app)
+    beta = app.array(g["stats_beta"], block_shape=(d + 1,))
+    s = m.fused_stats(Xb, yb, beta, True)
+    vals = app.km.get(s)
+    p = d + 1
+    H, gr, obj = vals[: p * p].reshape(p, p), vals[p * p: p * p + p], vals[p * p + p]
+    assert rel_err(gr, g["stats_g"]) < STAT_TOL
+    assert rel_err(H, g["stats_H"]) < STAT_TOL
+    assert rel_err(obj, g["stats_obj"]) < STAT_TOL
+    assert np.array_equal(H, H.T)
+
+
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("tag,cls,ykey,kw", [
+    ("lin_newton", "LinearRegression", "y_lin", dict(solver="newton", max_iter=3)),
+    ("lin_lbfgs", "LinearRegression", "y_lin", dict(solver="lbfgs", max_iter=8)),
+    ("ridge_newton", "Ridge", "y_lin", dict(solver="newton", alpha=0.5, max_iter=3)),
+    ("poi_newton", "PoissonRegression", "y_poi", dict(solver="newton", max_iter=6)),
+    ("poi_lbfgs", "PoissonRegression", "y_poi", dict(solver="lbfgs", max_iter=6)),
+])
+def test_linear_poisson(app, fused, tag, cls, ykey, kw):
+    from nums_b200 import glms
+    g = load_golden("glm_linear_poisson_d8")
+    m, _, _ = fit_dev(app, getattr(glms, cls), g["X"], g[ykey], int(g["row_block"]), fused=fused, **kw)
+    coef_close(m, g[tag + "_beta"], g[tag + "_beta0"], 1e-7 if "lbfgs" in tag else COEF_TOL)
+
+
+# ------------------------------------------------------------------------------------------------
+# GLM: seeded comparisons with the oracle across the kernel's column-width configurations
+# ------------------------------------------------------------------------------------------------
+def raw_stats(n, d, family, ydtype, ldx=None, seed=0):
+    """nb_glm_stats through the C ABI on one block -> (H, g, obj) and the oracle's."""
+    from nums_b200 import device as dv, fused
+    from nums_b200.device import DeviceBlock
+    rng = np.random.default_rng(seed + d)
+    X = rng.standard_normal((n, d)) / np.sqrt(d)
+    beta = rng.standard_normal(d + 1) * 0.5
+    if family == "logistic":
+        y = (rng.random(n) < 0.4).astype(ydtype)
+    elif family == "poisson":
+        y = rng.poisson(1.5, n).astype(ydtype)
+    else:
+        y = rng.standard_normal(n).astype(ydtype)
+    if ldx is None:
+        Xd = dv.from_numpy(X, 0)
+    else:   # a row-strided window: X is the left part of a wider block
+        wide = np.zeros((n, ldx))
+        wide[:, :d] = X
+        Xd = DeviceBlock(dv.from_numpy(wide, 0).t[:, :d])
+    s = dv.to_numpy(fused.glm_stats(Xd, dv.from_numpy(y, 0), dv.from_numpy(beta, 0), family, True))
+    p = d + 1
+    model = oglm.BlockedGLM(family, [X], [y])
+    fwd = model.forward(beta)
+    return (s[: p * p].reshape(p, p), s[p * p: p * p + p], s[p * p + p]), \
+           (model.hessian(beta, fwd), model.gradient(beta, fwd), model.objective(beta, fwd))
+
+
+@pytest.mark.parametrize("n,d", [(10_000, 1), (50_001, 2), (9_999, 7), (20_000, 8), (20_003, 33), (30_000, 64),
+                                 (10_000, 100), (40_000, 256), (8_000, 300), (6_000, 513), (3_000, 1024),
+                                 (1_500, 1500)])
+def test_glm_stats_vs_oracle_logistic(app, n, d):
+    (H, g, obj), (H0, g0, obj0) = raw_stats(n, d, "logistic", np.int64)
+    assert rel_err(g, g0) < STAT_TOL
+    assert rel_err(H, H0) < STAT_TOL
+    assert rel_err(obj, obj0) < STAT_TOL
+    assert np.array_equal(H, H.T)
+
+
+@pytest.mark.parametrize("family,ydtype", [("linear", np.float64), ("poisson", np.int64), ("poisson", np.float64)])
+@pytest.mark.parametrize("n,d,ldx", [(12_345, 5, None), (12_345, 40, None), (5_000, 129, None), (7_000, 31, 37),
+                                     (7_000, 96, 101)])
+def test_glm_stats_families_and_strides(app, family, ydtype, n, d, ldx):
+    (H, g, obj), (H0, g0, obj0) = raw_stats(n, d, family, ydtype, ldx)
+    assert rel_err(g, g0) < STAT_TOL
+    assert rel_err(H, H0) < STAT_TOL
+    assert rel_err(obj, obj0) < STAT_TOL
+
+
+def test_glm_edge_cases(app):
+    """ragged last block, a single row, and an empty row block"""
+    from nums_b200.glms import LogisticRegression
+    rng = np.random.default_rng(9)
+    X = rng.standard_normal((1003, 6))
+    y = (X[:, 0] + 0.3 * rng.standard_normal(1003) > 0).astype(np.int64)
+    want, _ = oglm.fit("logistic", X, y, 250, solver="newton", penalty="l2", lam=1.0, max_iter=20)
+    m, _, _ = fit_dev(app, LogisticRegression, X, y, 250, solver="newton", penalty="l2", C=1.0, max_iter=20)
+    coef_close(m, want[:-1], want[-1])
+    (H, g, obj), (H0, g0, obj0) = raw_stats(1, 9, "logistic", np.int64)
+    assert rel_err(H, H0) < STAT_TOL and rel_err(g, g0) < STAT_TOL
+    from nums_b200 import device as dv, fused
+    s = dv.to_numpy(fused.glm_stats(dv.from_numpy(np.zeros((0, 12)), 0), dv.from_numpy(np.zeros(0), 0),
+                                    dv.from_numpy(np.ones(13), 0), "logistic", True))
+    assert np.all(s == 0.0)
+
+
+def test_newton_full_fit_d256_vs_oracle(app):
+    """A 10^5 x 256 slice of BASELINE config 4 (delta = 2*sqrt(2/256)), 4 row blocks, to convergence."""
+    from nums_b200.glms import LogisticRegression
+    rng = np.random.default_rng(1337)
+    n, d = 100_000, 256
+    X = rng.standard_normal((n, d))
+    X[n // 2:] += 2.0 * np.sqrt(2.0 / d)
+    y = np.concatenate([np.zeros(n // 2, dtype=np.int64), np.ones(n // 2, dtype=np.int64)])
+    trace = []
+    want, it = oglm.fit("logistic", X, y, n // 4, solver="newton", penalty="l2", lam=0.1, trace=trace)
+    m, _, _ = fit_dev(app, LogisticRegression, X, y, n // 4, solver="newton", penalty="l2", C=10)
+    coef_close(m, want[:-1], want[-1])
+    assert m.n_iter_ == it
+
+
+def test_fused_equals_unfused_on_device(app):
+    """The fused passes and the op-by-op path through the generic kernels agree (1e-10)."""
+    from nums_b200.glms import LogisticRegression
+    rng = np.random.default_rng(21)
+    X = rng.standard_normal((6000, 40))
+    y = (rng.random(6000) < 0.5).astype(np.int64)
+    a, _, _ = fit_dev(app, LogisticRegression, X, y, 1500, fused=True, solver="newton", penalty="l2", C=3.0, max_iter=5)
+    b, _, _ = fit_dev(app, LogisticRegression, X, y, 1500, fused=False, solver="newton", penalty="l2", C=3.0, max_iter=5)
+    assert rel_err(a._beta.get(), b._beta.get()) < STAT_TOL
+
+
+# ------------------------------------------------------------------------------------------------
+# full-size properties (BASELINE sizes): size-independent invariants instead of an oracle run
+# ------------------------------------------------------------------------------------------------
+def test_full_size_vector_properties(app):
+    """10^8-element arrays (BASELINE config 2): dot of a constant, sum / argmax / where of a permutation."""
+    from nums_b200 import cuda_kernel
+    n = 10 ** 8
+    nblk = 8
+    rb = n // nblk
+    c = app.array(np.full(rb, 0.5), block_shape=(rb,))
+    whole = app.concatenate([c] * nblk, axis=0)
+    assert float((whole.T @ whole).get()) == n * 0.25                 # exact in float64
+    p_host = cuda_kernel.block_rng(1337, 0).permutation(n)
+    p = app.array(p_host, block_shape=(rb,))
+    assert int(app.sum(p).get()) == n * (n - 1) // 2                   # exact int64
+    am = int(app.argmax(p).get())
+    assert p_host[am] == n - 1
+    idx = app.where(p == n // 2)[0].get()
+    assert idx.shape == (1,) and p_host[idx[0]] == n // 2
+    sq = (p * p) % 7
+    assert int(app.max(sq).get()) <= 6 and int(app.min(sq).get()) >= 0
+
+
+def test_full_size_glm_pass_properties(app):
+    """One fused pass on a 2*10^6 x 256 block (4 GB): H symmetric, H = sum of two half passes
+    (additivity over row blocks), g = X^T r linear in y."""
+    from nums_b200 import device as dv, fused
+    from nums_b200.device import DeviceBlock
+    n, d = 2_000_000, 256
+    rng = np.random.default_rng(4)
+    chunk = rng.standard_normal((n // 8, d))
+    X = dv.empty((n, d), np.float64, 0)
+    for i in range(8):
+        dv.copy_into(X.t[i * (n // 8):(i + 1) * (n // 8)], dv.from_numpy(chunk * (1.0 + 0.01 * i), 0).t)
+    y = dv.from_numpy((rng.random(n) < 0.5).astype(np.int64), 0)
+    beta = dv.from_numpy(rng.standard_normal(d + 1) * 0.05, 0)
+    p = d + 1
+    full = dv.to_numpy(fused.glm_stats(X, y, beta, "logistic", True))
+    h = n // 2
+    a = dv.to_numpy(fused.glm_stats(DeviceBlock(X.t[:h]), DeviceBlock(y.t[:h]), beta, "logistic", True))
+    b = dv.to_numpy(fused.glm_stats(DeviceBlock(X.t[h:]), DeviceBlock(y.t[h:]), beta, "logistic", True))
+    H = full[: p * p].reshape(p, p)
+    assert np.array_equal(H, H.T)
+    assert rel_err(a + b, full) < STAT_TOL
+    assert np.all(np.linalg.eigvalsh(H) > 0)

@@ -1,0 +1,201 @@
+"""CPU-only checks: the C-ABI library loads and exports what include/nums_b200.h declares, the host
+logic (dtype resolution, broadcasting, block shapes, placement) agrees with NumPy / the reference,
+and the product refuses to run without a GPU."""
+import ast
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, load_golden
+from nums_b200 import _lib, build
+from nums_b200 import hostlogic as hl
+from nums_b200.grid import ArrayGrid, CyclicDeviceGrid, gpu_devices
+from nums_b200.kernel_manager import KernelManager
+
+REF = "/root/reference"
+
+
+def header_functions():
+    text = open(os.path.join(ROOT, "include", "nums_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(nb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    build.build_library()
+    lib = ctypes.CDLL(build.LIB_PATH)
+    names = header_functions()
+    assert len(names) >= 30
+    for name in names:
+        assert hasattr(lib, name), "libnumsb200.so does not export %s" % name
+    assert sorted(_lib.SIGNATURES) == names
+    lib.nb_version.restype = ctypes.c_int
+    assert lib.nb_version() == 1
+
+
+def test_scratch_queries_need_no_gpu():
+    lib = _lib.load()
+    assert lib.nb_glm_stats_len(256) == 257 * 257 + 257 + 1
+    assert lib.nb_where_chunks(10 ** 8) == -(-10 ** 8 // 4096)
+    assert lib.nb_reduce_scratch_bytes(1, 10 ** 8, 1) > 0
+    assert lib.nb_reduce_scratch_bytes(10 ** 6, 4, 1) == 0
+    assert lib.nb_inv_scratch_bytes(257) >= 257 * 257 * 8
+
+
+def test_product_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from nums_b200.app import make_app
+    with pytest.raises(_lib.NumsB200Error):
+        make_app()
+
+
+BOPS = ["add", "sub", "mul", "truediv", "floor_divide", "mod", "pow", "lt", "eq", "bitwise_and", "left_shift",
+        "maximum", "fmin", "arctan2", "logaddexp", "logical_or"]
+
+
+@pytest.mark.parametrize("op", BOPS)
+def test_bop_dtype_resolution_matches_numpy(op):
+    name = hl.canonical_bop(op)
+    for da in (np.float64, np.int64, np.bool_):
+        for db in (np.float64, np.int64, np.bool_):
+            a, b = np.array(1, dtype=da), np.array(2, dtype=db)
+            try:
+                want = getattr(np, name)(a, b).dtype   # what the reference does (array/utils.py:40-51)
+            except TypeError:
+                with pytest.raises(TypeError):
+                    hl.resolve_bop(op, da, db)
+                continue
+            if want not in (np.dtype(np.float64), np.dtype(np.int64), np.dtype(np.bool_)):
+                with pytest.raises(NotImplementedError):
+                    hl.resolve_bop(op, da, db)
+                continue
+            _, cdt, odt = hl.resolve_bop(op, da, db)
+            assert odt == want
+            assert cdt in (hl.NB_F64, hl.NB_I64, hl.NB_BOOL)
+
+
+def test_uop_dtype_resolution_matches_numpy():
+    for op in ["exp", "abs", "negative", "sqrt", "sign", "isnan", "invert", "ceil", "fabs", "square"]:
+        for dt in (np.float64, np.int64):
+            try:
+                want = getattr(np, op)(np.array(1, dtype=dt)).dtype
+            except TypeError:
+                continue
+            assert hl.resolve_uop(op, dt)[2] == want
+
+
+def test_broadcast_and_collapse():
+    shape, sa, sb = hl.broadcast_geometry((6, 1), (1, 1), (6, 4), (4, 1))
+    assert shape == (6, 4) and sa == (1, 0) and sb == (4, 1)
+    shape, sa, sb = hl.broadcast_geometry((), (), (5,), (1,))
+    assert shape == (5,) and sa == (0,) and sb == (1,)
+    with pytest.raises(ValueError):
+        hl.broadcast_geometry((3,), (1,), (4,), (1,))
+    # contiguous same-shape operands collapse to one axis
+    assert hl.collapse_dims((2, 3, 4), (12, 4, 1), (12, 4, 1)) == ((24,), (1,), (1,))
+    # transposed 2-d operand cannot be merged
+    cs = hl.collapse_dims((3, 4), (4, 1), (1, 3))
+    assert cs[0] == (3, 4)
+    assert hl.reduce_geometry((3, 4, 5), 1) == (3, 4, 5)
+    assert hl.reduce_geometry((3, 4, 5), None) == (1, 60, 1)
+    assert hl.reduce_geometry((7,), 0) == (1, 7, 1)
+
+
+def test_reduce_out_dtype():
+    for op in ("sum", "min", "max", "all", "any"):
+        for dt in (np.float64, np.int64, np.bool_):
+            want = getattr(np, op)(np.array([0, 1], dtype=dt)).dtype
+            assert hl.reduce_out_dtype(op, dt) == want
+
+
+def test_block_shape_rule_matches_reference():
+    g = load_golden("block_shapes")
+    for i in range(len(g["case_ndim"])):
+        nd = int(g["case_ndim"][i])
+        shape = tuple(int(v) for v in g["case_shape"][i][:nd])
+        got = KernelManager.compute_block_shape_static(shape, np.dtype(str(g["case_dtype"][i])),
+                                                       tuple(int(v) for v in g["case_cluster"][i]),
+                                                       int(g["case_cores"][i]))
+        assert got == tuple(int(v) for v in g["block_shape"][i][:nd])
+    # the configurations of BASELINE.json
+    assert KernelManager.compute_block_shape_static((10 ** 8, 256), np.float64, (8, 1), 8) == (12500000, 256)
+    assert KernelManager.compute_block_shape_static((10 ** 6, 2), np.float64, (8, 1), 8) == (10 ** 6, 2)
+
+
+def test_grid_and_static_placement():
+    grid = ArrayGrid((10, 7), (4, 7), "float64")
+    assert grid.grid_shape == (3, 1)
+    assert grid.get_block_shape((2, 0)) == (2, 7)
+    assert grid.get_slice_tuples((1, 0)) == [(4, 8), (0, 7)]
+    dg = CyclicDeviceGrid((4, 1), "gpu", gpu_devices(4))
+    # row block i of a (G,1)-blocked array lives on GPU i: static placement
+    assert [dg.get_device((i, 0), (4, 1)).device for i in range(4)] == [0, 1, 2, 3]
+    assert dg.get_device((5, 0), (8, 1)).device == 1
+    assert dg.get_device((2,), (4,)).device == 2
+    for world in (1, 2, 3, 8):
+        n = 1001
+        spans = [hl.row_shard(n, world, r) for r in range(world)]
+        assert spans[0][0] == 0 and spans[-1][1] == n
+        assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+        ag = ArrayGrid((n,), (-(-n // world),), "float64")
+        assert [tuple(ag.get_slice_tuples((r,))[0]) for r in range(ag.grid_shape[0])] == \
+            [s for s in spans if s[1] > s[0]]
+
+
+def _class_methods(path, cls_name):
+    tree = ast.parse(open(path).read())
+    for node in tree.body:
+        if isinstance(node, ast.ClassDef) and node.name == cls_name:
+            out = {}
+            for fn in node.body:
+                if isinstance(fn, ast.FunctionDef):
+                    args = [a.arg for a in fn.args.args + fn.args.kwonlyargs]
+                    if fn.args.vararg:
+                        args.append(fn.args.vararg.arg)
+                    out[fn.name] = args
+            return out
+    raise KeyError(cls_name)
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference checkout not present")
+def test_kernel_module_satisfies_reference_interface():
+    """What nums.core.backends.utils.check_implementation (:74-87) enforces, checked from the
+    reference's source without importing it."""
+    import inspect
+    from nums_b200 import cuda_kernel
+    iface = _class_methods(os.path.join(REF, "nums/core/kernel/kernel_interface.py"), "Kernel")
+    assert len(iface) == 39
+    for name, args in iface.items():
+        assert hasattr(cuda_kernel.KernelCls, name), "KernelCls.%s missing" % name
+        have = inspect.getfullargspec(getattr(cuda_kernel.KernelCls, name))
+        have_names = set(have.args + have.kwonlyargs + ([have.varargs] if have.varargs else []))
+        for a in args:
+            if a in ("self", "syskwargs"):
+                continue
+            assert a in have_names, "KernelCls.%s lacks parameter %s" % (name, a)
+    assert hasattr(cuda_kernel, "RNG") and hasattr(cuda_kernel.RNG, "new_block_rng_params")
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference checkout not present")
+def test_backend_satisfies_reference_interface():
+    from nums_b200.cuda_backend import CudaBackend
+    iface = _class_methods(os.path.join(REF, "nums/core/backends/base.py"), "Backend")
+    assert len(iface) == 12
+    for name in iface:
+        assert callable(getattr(CudaBackend, name, None)), "CudaBackend.%s missing" % name
+
+
+def test_rng_stream_matches_reference_rule():
+    from nums_b200 import cuda_kernel
+    from oracle import np_kernel as ok
+    rng = cuda_kernel.RNG(1337)
+    p0, p1 = rng.new_block_rng_params(), rng.new_block_rng_params()
+    assert p0 == (1337, 0) and p1 == (1337, 1)
+    a = cuda_kernel.block_rng(*p1).normal(0.0, 1.0, 5)
+    b = ok.random_block(p1, "normal", (0.0, 1.0, 5), (5,), np.float64)
+    np.testing.assert_array_equal(a, b)

@@ -1,0 +1,106 @@
+"""Pins the oracle (oracle/) against vectors produced by the reference itself (tests/golden)."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, rel_err
+from oracle import glm as oglm
+from oracle import np_kernel as ok
+
+# float64 results of the oracle and of the reference come from the same NumPy calls in the same
+# order, so they are expected to agree to the last bit; the tolerance only absorbs BLAS threading.
+TOL = 1e-12
+
+
+def test_readme_logistic_newton():
+    g = load_golden("glm_readme")
+    beta, it = oglm.fit("logistic", g["X"], g["y"], int(g["row_block"]), solver="newton-cg", penalty="l2",
+                        lam=1.0 / 10)
+    assert rel_err(beta[:-1], g["beta"]) < TOL
+    assert abs(beta[-1] - g["beta0"]) < TOL * abs(g["beta0"])
+    assert it < 100
+
+
+@pytest.mark.parametrize("tag,kw", [
+    ("newton_none", dict(solver="newton", penalty=None, max_iter=4)),
+    ("newton_l2", dict(solver="newton", penalty="l2", lam=0.5, max_iter=6)),
+    ("lbfgs_l2", dict(solver="lbfgs", penalty="l2", lam=0.5, max_iter=6)),
+    ("gd_l2", dict(solver="gd", penalty="l2", lam=0.5, max_iter=5, lr=1e-4)),
+])
+def test_logistic_d32(tag, kw):
+    g = load_golden("glm_logistic_d32")
+    beta, _ = oglm.fit("logistic", g["X"], g["y"], int(g["row_block"]), **kw)
+    assert rel_err(beta[:-1], g[tag + "_beta"]) < 1e-10
+    assert abs(beta[-1] - g[tag + "_beta0"]) < 1e-10 * max(1.0, abs(g[tag + "_beta0"]))
+
+
+def test_logistic_stats_d32():
+    g = load_golden("glm_logistic_d32")
+    rb = int(g["row_block"])
+    m = oglm.BlockedGLM("logistic", oglm.split_rows(g["X"], rb), oglm.split_rows(g["y"], rb))
+    beta = g["stats_beta"]
+    fwd = m.forward(beta)
+    assert rel_err(m.gradient(beta, fwd), g["stats_g"]) < TOL
+    assert rel_err(m.hessian(beta, fwd), g["stats_H"]) < TOL
+    assert rel_err(m.objective(beta, fwd), g["stats_obj"]) < TOL
+
+
+@pytest.mark.parametrize("tag,family,ykey,kw", [
+    ("lin_newton", "linear", "y_lin", dict(solver="newton", max_iter=3)),
+    ("lin_lbfgs", "linear", "y_lin", dict(solver="lbfgs", max_iter=8)),
+    ("ridge_newton", "linear", "y_lin", dict(solver="newton", penalty="l2", lam=0.5, max_iter=3)),
+    ("poi_newton", "poisson", "y_poi", dict(solver="newton", max_iter=6)),
+    ("poi_lbfgs", "poisson", "y_poi", dict(solver="lbfgs", max_iter=6)),
+])
+def test_linear_poisson(tag, family, ykey, kw):
+    g = load_golden("glm_linear_poisson_d8")
+    beta, _ = oglm.fit(family, g["X"], g[ykey], int(g["row_block"]), **kw)
+    assert rel_err(beta[:-1], g[tag + "_beta"]) < 1e-9
+    assert abs(beta[-1] - g[tag + "_beta0"]) < 1e-9 * max(1.0, abs(g[tag + "_beta0"]))
+
+
+INT_OPS = ["add", "sub", "mul", "truediv", "floor_divide", "mod", "fmod", "maximum", "minimum", "lt", "le", "gt",
+           "ge", "eq", "ne", "bitwise_and", "bitwise_or", "bitwise_xor", "left_shift", "right_shift", "gcd", "lcm",
+           "logical_and", "logical_or", "logical_xor"]
+
+
+def test_kernels_match_reference():
+    g = load_golden("kernels")
+    with np.errstate(all="ignore"):
+        for op in INT_OPS:
+            r = ok.bop(op, g["ia"], g["ib"])
+            assert r.dtype == g["i_" + op].dtype, op
+            np.testing.assert_array_equal(r, g["i_" + op], err_msg=op)
+        for key in [k for k in g if k.startswith("f_")]:
+            np.testing.assert_array_equal(ok.bop(key[2:], g["fa"], g["fb"]), g[key], err_msg=key)
+        for key in [k for k in g if k.startswith("u_")]:
+            np.testing.assert_array_equal(ok.map_uop(key[2:], g["ua"]), g[key], err_msg=key)
+    np.testing.assert_array_equal(ok.reduce_axis("sum", g["imat"], 0, False, False), g["red_sum_ax0_int"])
+    assert ok.reduce_axis("sum", g["imat"], 0, False, False).dtype == np.float64      # quirk Q1
+    assert ok.reduce_axis("sum", g["imat"], None, False, False).dtype == np.int64
+    r0 = ok.arg_op("argmax", np.array([5.0, 1.0]), slice(0, 2))
+    r1 = ok.arg_op("argmax", np.array([5.0, 0.0]), slice(2, 4), *r0)
+    assert [r0[0], r1[0]] == list(g["arg_chain"]) == [0, 2]                             # quirk Q2
+    w = ok.where(g["where_cond"], None, None, [(10, 15), (100, 106)])
+    np.testing.assert_array_equal(w[0], g["where_rows"])
+    np.testing.assert_array_equal(w[1], g["where_cols"])
+    np.testing.assert_array_equal(ok.bop("tensordot", g["A"], g["A"], True, False, 1), g["mm_T"])
+    np.testing.assert_array_equal(ok.inv(g["S"]), g["S_inv"])
+
+
+def test_blockarray_level():
+    g = load_golden("blockarray")
+    rb = int(g["row_block"])
+    xb = oglm.split_rows(g["x"], rb)
+    dot = oglm.tree_sum([np.matmul(b, b) for b in xb])
+    assert rel_err(dot, g["dot"]) < TOL
+    pb = oglm.split_rows(g["p"], rb)
+    hits = []
+    for i, b in enumerate(pb):
+        r = ok.where(b == len(g["p"]) // 2, None, None, [(i * rb, (i + 1) * rb)])
+        hits.append(r[0])
+    np.testing.assert_array_equal(np.concatenate(hits), g["where_idx"])
+    red = (None, None)
+    for i, b in enumerate(pb):
+        red = ok.arg_op("argmax", b, slice(i * rb, (i + 1) * rb), *red)
+    assert red[0] == g["argmax_p"]
+    assert oglm.tree_sum([np.sum(b) for b in pb]) == g["sum_p"]
