@@ -238,11 +238,17 @@ k_gemm(const GemmArgs g) {
       for (int j = 0; j < FN; j++) {
         int64_t r = m0 + wm * WM + i * 8 + lq, c = n0 + wn * WN + j * 8 + 2 * lr;
         if (r < g.m) {
-          if (c < g.n) g.c[r * g.ldc + c] = acc[i][j][0];
-          if (c + 1 < g.n) g.c[r * g.ldc + c + 1] = acc[i][j][1];
-          if (g.sym && tm != tn) {   // mirror the off-diagonal tile
-            if (c < g.n) g.c[c * g.ldc + r] = acc[i][j][0];
-            if (c + 1 < g.n) g.c[(c + 1) * g.ldc + r] = acc[i][j][1];
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            int64_t cc = c + e;
+            if (cc >= g.n) continue;
+            if (g.sym) {
+              // only the upper triangle is authoritative; the lower one is its mirror image, so the
+              // result is exactly symmetric
+              if (r <= cc) { g.c[r * g.ldc + cc] = acc[i][j][e]; if (r != cc) g.c[cc * g.ldc + r] = acc[i][j][e]; }
+            } else {
+              g.c[r * g.ldc + cc] = acc[i][j][e];
+            }
           }
         }
       }
@@ -261,7 +267,8 @@ k_gemm_reduce(const GemmArgs g) {
     int lr_ = (int)(r - (int64_t)tm * BM), lc = (int)(c - (int64_t)tn * BN);
     int t;
     if (g.sym) {
-      if (tn < tm) { int x = tm; tm = tn; tn = x; x = lr_; lr_ = lc; lc = x; }
+      // read every element from the upper triangle (r <= c): exact symmetry
+      if (c < r) { int x = tm; tm = tn; tn = x; x = lr_; lr_ = lc; lc = x; }
       // index of (tm, tn) in the row-by-row upper-triangular list
       t = tm * g.tiles_n - (tm * (tm - 1)) / 2 + (tn - tm);
     } else {

@@ -254,7 +254,8 @@ static RedPlan plan_reduce(int64_t outer, int64_t len, int64_t inner) {
 
 template <int RED, typename T>
 static int run_reduce(int device, int64_t outer, int64_t len, int64_t inner, const void* a, int adt, void* out,
-                      int odt, int acc_dt, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+                      int odt, int acc_dt, void* scratch, size_t scratch_bytes, cudaStream_t st,
+                      bool second_stage = false) {
   const int sms = dev_info(device).sms;
   if (inner == 1 && len <= 16 && outer >= 1024) {
     int grid = grid_for(device, outer, RED_THREADS, 1);
@@ -270,6 +271,7 @@ static int run_reduce(int device, int64_t outer, int64_t len, int64_t inner, con
     return 0;
   }
   RedPlan p = plan_reduce(outer, len, inner);
+  if (second_stage) { p.S = 1; p.chunk = len; }   // partials of stage one are reduced in one go
   void* dst = out;
   int dst_dt = odt;
   if (p.S > 1) {
@@ -290,7 +292,7 @@ static int run_reduce(int device, int64_t outer, int64_t len, int64_t inner, con
   if (p.S > 1) {
     // second stage: [outer, S, inner] -> [outer, inner]; S <= 592 so no further split is needed
     return run_reduce<RED == NB_RNANSUM ? NB_RSUM : RED, T>(device, outer, p.S, inner, scratch, dst_dt, out, odt,
-                                                           acc_dt, nullptr, 0, st);
+                                                           acc_dt, nullptr, 0, st, true);
   }
   return 0;
 }

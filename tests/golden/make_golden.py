@@ -91,7 +91,7 @@ def main():
          pred=model.predict(X).get())
 
     # ---------------------------------------------------------------- logistic d=32, 4 row blocks
-    rs = app.random
+    rs = app.random_state(1337)      # block j draws from PCG64(1337).jumped(j)
     n, d, rb = 4096, 32, 1024
     Xb = rs.normal(shape=(n, d), block_shape=(rb, d))
     w_true = np.linspace(-1.0, 1.0, d)
@@ -247,9 +247,10 @@ def main():
     # ---------------------------------------------------------------- BlockArray level (cfg 2 scaled down)
     nps.random.seed(1337)
     n = 100000
-    x = app.random.random(shape=(n,), block_shape=(n // 4,))
+    rs2 = app.random_state(1337)
+    x = rs2.random(shape=(n,), block_shape=(n // 4,))
     dot = (x.T @ x).get()
-    p = app.random.permutation(n, n // 4)
+    p = rs2.permutation(n, n // 4)
     idx = app.where(p == n // 2)
     s = app.sum(p)
     am, amin = app.argop("argmax", p), app.argop("argmin", x)
