@@ -35,6 +35,7 @@ SIGNATURES = {
     "nb_copy_strided": (c_int, [c_int, c_int, P_I64, c_int, c_vp, P_I64, c_vp, P_I64, c_vp]),
     "nb_reduce_scratch_bytes": (c_sz, [c_i64, c_i64, c_i64]),
     "nb_reduce": (c_int, [c_int, c_int, c_i64, c_i64, c_i64, c_vp, c_int, c_vp, c_int, c_int, c_vp, c_sz, c_vp]),
+    "nb_reduce_static": (c_int, [c_int, c_int, c_i64, c_i64, c_i64, c_vp, c_int, c_vp, c_int, c_int, c_vp]),
     "nb_bop_reduce": (c_int, [c_int, c_int, c_i64, c_vp, c_vp, c_vp, c_int, c_vp]),
     "nb_sum_reduce": (c_int, [c_int, c_int, c_i64, C.POINTER(c_vp), c_vp, c_int, c_vp]),
     "nb_argop_scratch_bytes": (c_sz, [c_i64]),

@@ -5,6 +5,7 @@
 // warp shuffles -> shared memory -> ordered second pass): no floating-point atomics, so results
 // are run-to-run identical.
 #include "common.cuh"
+#include <mutex>
 
 namespace nb {
 
@@ -703,6 +704,73 @@ int nb_where_fill(int device, int64_t n, const void* cond_d, int cond_dt, int nd
   k_where_fill<<<grid, 256, 0, st>>>(n, cond_d, cond_dt, nchunks, chunk_counts_d, wo);
   NB_LAUNCH_CHECK();
   return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// nb_reduce_static: the reduction for callers that cannot allocate device memory
+// ------------------------------------------------------------------------------------------------
+// Some users of this library only ever hold the input and output pointers somebody else gave them:
+// a cgo/JNI/ctypes host that wraps buffers owned by another runtime's memory pool, a plug-in running
+// inside a service whose HBM budget is fixed at start-up, or code sitting between the begin and end
+// of a stream capture, where cudaMalloc is not permitted.  They have nowhere to get the split-reduction
+// scratch from, so this variant keeps it inside the library: a fixed array in device memory that is part
+// of the loaded module (every GPU that loads libnumsb200.so carries these NB_REDUCE_STATIC_BYTES until
+// the process exits).
+//
+// `g_reduce_static` below is a host-side handle in host code, not an address a kernel can use; the
+// real device address is looked up once per device with cudaGetSymbolAddress while that device is
+// current, and cached.
+static __device__ __align__(256) unsigned char g_reduce_static[NB_REDUCE_STATIC_BYTES];
+
+namespace nb {
+static void* g_static_addr[64];
+static bool g_static_ready[64];
+static std::mutex g_static_mu;
+
+// Resolves the device address of g_reduce_static on `device` (which must be the current device).
+static int static_scratch_for(int device, void** out) {
+  NB_REQUIRE(device >= 0 && device < 64, "nb_reduce_static: device %d out of range", device);
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ready[device]) {
+    void* p = nullptr;
+    NB_CHECK(cudaGetSymbolAddress(&p, g_reduce_static));
+    NB_REQUIRE(p != nullptr, "nb_reduce_static: cudaGetSymbolAddress returned a null address");
+    g_static_addr[device] = p;
+    g_static_ready[device] = true;
+  }
+  *out = g_static_addr[device];
+  return 0;
+}
+}  // namespace nb
+
+extern "C" {
+
+// Same contract and same kernels as nb_reduce, minus the scratch arguments.
+//  * The first call on each device performs the address look-up described above.  Make that first call
+//    outside of any stream capture (it is an ordinary synchronous runtime query, not stream work).
+//  * A reduction whose split needs more than NB_REDUCE_STATIC_BYTES (1 MiB) is refused with an error;
+//    use nb_reduce with caller-provided scratch for those (nb_reduce_scratch_bytes tells the size).
+//  * All calls on a device share the one array and it keeps whatever the previous call left there.
+//    Nothing in it has to start at zero: stage one overwrites every partial that stage two reads.
+//    Because it is shared, two calls whose kernels can overlap on the GPU (different streams, or
+//    different host threads on different streams) race on it; issue them on one stream or serialise them.
+//  * No cudaMalloc / cudaFree / allocating library routine is called on this path.
+int nb_reduce_static(int device, int red, int64_t outer, int64_t len, int64_t inner, const void* a_d, int adt,
+                     void* out_d, int odt, int acc_dt, void* stream) {
+  NB_ENTER(device);
+  NB_REQUIRE(outer >= 0 && len >= 1 && inner >= 1, "nb_reduce_static: empty reduction axis (len=%lld)", (long long)len);
+  if (outer == 0) return 0;
+  const size_t need = nb_reduce_scratch_bytes(outer, len, inner);
+  NB_REQUIRE(need <= (size_t)NB_REDUCE_STATIC_BYTES,
+             "nb_reduce_static: this reduction needs %zu bytes of scratch but the built-in buffer holds %u; "
+             "call nb_reduce with your own scratch instead", need, (unsigned)NB_REDUCE_STATIC_BYTES);
+  void* scratch = nullptr;
+  int rc = static_scratch_for(device, &scratch);
+  if (rc) return rc;
+  return dispatch_reduce(device, red, outer, len, inner, a_d, adt, out_d, odt, acc_dt, scratch,
+                         NB_REDUCE_STATIC_BYTES, st);
 }
 
 }  // extern "C"
