@@ -236,16 +236,16 @@ def run_ours(args):
     ms_step = ms_total / K
     value = world * algorithmic_bytes(n, d) / (ms_step * 1e-3) / 1e9
 
-    # ---- dominant kernel alone (the FP64 DMMA weighted Gram of pass 2), timed on its stream
+    # ---- dominant kernel alone: the fused single-pass statistics kernel (k_glm_fused + its finish),
+    # called through the C ABI and timed with CUDA events on the stream it is launched on
     st = dv.stream_ptr(local)
-    wbuf = dv.empty((n,), np.float64, local)
-    _lib.check(lib.nb_fill(local, n, wbuf.ptr, wbuf.code, 0.25, 0, st))
-    G = dv.empty((d, d), np.float64, local)
-    sc = dv.scratch(lib.nb_matmul_scratch_bytes(local, d, d, n), local)
+    beta_d = dv.from_numpy(np.full(p, 0.01), local)
+    stats_d = dv.empty((lib.nb_glm_stats_len(d),), np.float64, local)
+    sc = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 1), local)
 
     def gram():
-        _lib.check(lib.nb_matmul_f64(local, d, d, n, X.ptr, 1, d, X.ptr, d, 1, wbuf.ptr, G.ptr, d,
-                                     sc.data_ptr(), sc.numel(), st))
+        _lib.check(lib.nb_glm_stats(local, 1, X.ptr, n, d, d, y.ptr, y.code, beta_d.ptr, 1, stats_d.ptr,
+                                    sc.data_ptr(), sc.numel(), st))
 
     for _ in range(3):
         gram()
@@ -259,7 +259,6 @@ def run_ours(args):
     torch.cuda.synchronize()
     gram_ms = g0.elapsed_time(g1) / reps
     # pass 1 alone (HBM-bound link / gradient pass = the L-BFGS evaluation)
-    beta_d = dv.from_numpy(np.full(p, 0.01), local)
     for _ in range(2):
         fused.glm_stats(X, y, beta_d, "logistic", False)
     torch.cuda.synchronize()
@@ -271,7 +270,7 @@ def run_ours(args):
     torch.cuda.synchronize()
     rows_ms = r0.elapsed_time(r1) / reps
     clocks = sampler.stop() if rank == 0 else None
-    del wbuf, G, sc
+    del stats_d, sc
 
     # ---- end to end through the public API with HOST buffers (upload + K iterations + read-back)
     e2e = None
@@ -344,20 +343,22 @@ def run_ours(args):
                    "rows_per_gpu": n, "d": d, "penalty": "l2", "C": 10, "l2_flush": L2_NOTE,
                    "step": "one Newton iteration: fused stats pass + all-reduce(p*p+p+1 f64) + Newton update + 8-byte read-back"},
         "fit_sec_per_iteration": ms_step * 1e-3,
-        "roofline": {"bound": "hbm", "kernel": "k_gemm (FP64 DMMA weighted Gram X^T diag(w) X, pass 2) + split-k reduce",
+        "roofline": {"bound": "hbm", "kernel": "k_glm_fused (single pass: eta, link, objective, g, upper-triangular X^T diag(w) X by FP64 DMMA) "
+                               "+ k_fused_finish, via nb_glm_stats",
                      "achieved": gram_bytes / (gram_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                      "frac": gram_bytes / (gram_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
                      "ms_per_launch": gram_ms,
-                     "note": "this pass is FP64-compute-bound at d=256 (intensity ~32 flop/B vs ~5.7 balance); "
-                             "see fp64 and pass1"},
+                     "note": "FP64-tensor-bound at d=256 (32 flop/B vs a balance of ~5.7): the DMMA ceiling is "
+                             "n*d*(d+1)/37.2e12 s = 18% of the HBM peak; see fp64 (tensor roofline) and pass1 (HBM-bound pass)"},
         "fp64": {"achieved_tflops_sym": gram_flops_sym / (gram_ms * 1e-3) / 1e12,
-                 "achieved_tflops_executed": 2.0 * n * (3 * 128 * 128 if d == 256 else d * d) / (gram_ms * 1e-3) / 1e12,
+                 "achieved_tflops_executed": 2.0 * n * 1024 * (((d + 31) // 32) * ((d + 31) // 32 + 1) // 2)
+                 / (gram_ms * 1e-3) / 1e12,
                  "peak_tflops": fp64_peak},
         "pass1": {"kernel": "k_glm_rows (eta/link/objective/gradient, HBM-bound)", "ms_per_launch": rows_ms,
                   "achieved": gram_bytes / (rows_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                   "frac": gram_bytes / (rows_ms * 1e-3) / 1e9 / hbm_peak},
         "clocks": clocks,
-        "gpu_launches": 7 * K,
+        "gpu_launches": 5 * K,
         "coef_checksum": float(np.sum(np.abs(km.get(beta.blocks[(0,)].oid)))),
     }
     if e2e is not None:

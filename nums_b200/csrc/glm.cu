@@ -11,46 +11,10 @@
 // The intercept column of GLM.fit (glms.py:124-135) is implicit: it is never stored.
 // All cross-thread sums are fixed-order (per-CTA partials in scratch, then an ordered second stage).
 #include "gemm.cuh"
+#include "glm_common.cuh"
+#include <stdlib.h>
 
 namespace nb {
-
-struct LinkOut { double resid, wgt, obj; };
-
-template <int FAMILY>
-__device__ __forceinline__ LinkOut glm_link(double eta, double y) {
-  LinkOut o;
-  if constexpr (FAMILY == NB_GLM_LOGISTIC) {
-    // glms.py:457-458 link_inv, :470 objective, :485 gradient residual, :495 hessian weights
-    double mu = 1.0 / (1.0 + exp(-eta));
-    o.resid = mu - y;
-    o.wgt = mu * (1.0 - mu);
-    o.obj = -(y * log(mu) + (1.0 - y) * log(1.0 - mu));
-  } else if constexpr (FAMILY == NB_GLM_POISSON) {
-    // glms.py:516-517, :531, :544, :548
-    double mu = exp(eta);
-    o.resid = mu - y;
-    o.wgt = mu;
-    o.obj = mu - y * eta;
-  } else {
-    // glms.py:283-284, :296, :311, :318
-    o.resid = eta - y;
-    o.wgt = 1.0;
-    double e = y - eta;
-    o.obj = e * e;
-  }
-  return o;
-}
-
-template <int FAMILY>
-__device__ __forceinline__ double glm_mu(double eta) {
-  if constexpr (FAMILY == NB_GLM_LOGISTIC) return 1.0 / (1.0 + exp(-eta));
-  else if constexpr (FAMILY == NB_GLM_POISSON) return exp(eta);
-  else return eta;
-}
-
-__device__ __forceinline__ double load_y(const void* y, int ydt, int64_t i) {
-  return ydt == NB_F64 ? ((const double*)y)[i] : (double)((const int64_t*)y)[i];
-}
 
 constexpr int GLM_THREADS = 256;
 
@@ -159,12 +123,6 @@ struct GlmRowsArgs {
   double* wbuf;        // n weights for pass 2 (null: not needed)
   double* partials;    // [gridDim.x][2*d + 3]
 };
-
-__device__ __forceinline__ LinkOut glm_link_rt(int family, double eta, double y) {
-  if (family == NB_GLM_LOGISTIC) return glm_link<NB_GLM_LOGISTIC>(eta, y);
-  if (family == NB_GLM_POISSON) return glm_link<NB_GLM_POISSON>(eta, y);
-  return glm_link<NB_GLM_LINEAR>(eta, y);
-}
 
 template <int NJ, int WPR, bool VEC>
 __global__ void __launch_bounds__(GLM_THREADS)
@@ -361,6 +319,22 @@ k_glm_predict(int family, const double* __restrict__ x, int64_t n, int64_t d, in
 // ------------------------------------------------------------------------------------------------
 static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+// glm_fused.cu
+bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
+size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
+int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
+                    int ydt, const double* beta, const double* wext, bool link, double* stats, void* scratch,
+                    size_t scratch_bytes, cudaStream_t st);
+// 0: two passes, pass 2 = triangular DMMA kernel (default); 1: single fused pass; 2: two passes, pass 2 = generic GEMM
+static int glm_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("NUMS_B200_GLM_MODE");
+    mode = e ? atoi(e) : 0;
+  }
+  return mode;
+}
+
 struct GlmLayout {
   size_t off_w, off_parts, off_gemm, total;
   int max_parts;
@@ -378,6 +352,10 @@ static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
   cur += align256((size_t)L.max_parts * per * sizeof(double));
   L.off_gemm = cur;
   if (want_hess && d >= 8) cur += align256(gemm_scratch_bytes(device, d, d, n));
+  if (want_hess && d >= 8 && d <= 256) {   // the triangular / single-pass kernels take their partials from the GEMM region
+    size_t f = L.off_gemm + align256(fused_scratch_bytes(device, n, d));
+    if (f > cur) cur = f;
+  }
   L.total = cur;
   return L;
 }
@@ -478,6 +456,10 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
       default: return launch_small_d<NB_GLM_LINEAR>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
     }
   }
+  const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);
+  if (tri_ok && glm_mode() == 1)
+    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, nullptr, true, stats_d,
+                           sc + L.off_gemm, L.total - L.off_gemm, st);
   GlmRowsArgs a;
   a.x = x_d; a.n = n; a.d = d; a.ldx = ldx; a.y = y_d; a.ydt = ydt; a.beta = beta_d;
   a.family = family; a.want_hess = want_hess;
@@ -491,6 +473,11 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   if (rc) return rc;
   k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 255) / 256), 256, 0, st>>>(d, nparts, parts, want_hess, stats_d);
   NB_LAUNCH_CHECK();
+  if (tri_ok && glm_mode() == 0) {
+    // pass 2: upper-triangular blocks of X^T diag(w) X by FP64 DMMA, mirrored -> exactly symmetric
+    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, false, stats_d,
+                           sc + L.off_gemm, L.total - L.off_gemm, st);
+  }
   if (want_hess) {
     // G = X^T diag(w) X into the top-left d x d of the p x p Hessian (row stride p)
     rc = gemm_f64(device, d, d, n, x_d, 1, ldx, x_d, ldx, 1, a.wbuf, stats_d, d + 1, sc + L.off_gemm,

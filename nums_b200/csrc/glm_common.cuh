@@ -1,0 +1,52 @@
+// Link functions of the GLM families, shared by glm.cu and glm_fused.cu.
+#pragma once
+#include "common.cuh"
+
+namespace nb {
+
+struct LinkOut { double resid, wgt, obj; };
+
+template <int FAMILY>
+__device__ __forceinline__ LinkOut glm_link(double eta, double y) {
+  LinkOut o;
+  if constexpr (FAMILY == NB_GLM_LOGISTIC) {
+    // glms.py:457-458 link_inv, :470 objective, :485 gradient residual, :495 hessian weights
+    double mu = 1.0 / (1.0 + exp(-eta));
+    o.resid = mu - y;
+    o.wgt = mu * (1.0 - mu);
+    o.obj = -(y * log(mu) + (1.0 - y) * log(1.0 - mu));
+  } else if constexpr (FAMILY == NB_GLM_POISSON) {
+    // glms.py:516-517, :531, :544, :548
+    double mu = exp(eta);
+    o.resid = mu - y;
+    o.wgt = mu;
+    o.obj = mu - y * eta;
+  } else {
+    // glms.py:283-284, :296, :311, :318
+    o.resid = eta - y;
+    o.wgt = 1.0;
+    double e = y - eta;
+    o.obj = e * e;
+  }
+  return o;
+}
+
+template <int FAMILY>
+__device__ __forceinline__ double glm_mu(double eta) {
+  if constexpr (FAMILY == NB_GLM_LOGISTIC) return 1.0 / (1.0 + exp(-eta));
+  else if constexpr (FAMILY == NB_GLM_POISSON) return exp(eta);
+  else return eta;
+}
+
+__device__ __forceinline__ double load_y(const void* y, int ydt, int64_t i) {
+  return ydt == NB_F64 ? ((const double*)y)[i] : (double)((const int64_t*)y)[i];
+}
+
+__device__ __forceinline__ LinkOut glm_link_rt(int family, double eta, double y) {
+  if (family == NB_GLM_LOGISTIC) return glm_link<NB_GLM_LOGISTIC>(eta, y);
+  if (family == NB_GLM_POISSON) return glm_link<NB_GLM_POISSON>(eta, y);
+  return glm_link<NB_GLM_LINEAR>(eta, y);
+}
+
+
+}  // namespace nb
