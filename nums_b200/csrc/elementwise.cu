@@ -254,12 +254,37 @@ __global__ void __launch_bounds__(EW_THREADS)
 k_bop_2d(int64_t rows, int64_t cols, const void* __restrict__ a, int adt, int64_t ars, int64_t acs,
          const void* __restrict__ b, int bdt, int64_t brs, int64_t bcs, void* __restrict__ out, int odt) {
   using R = typename BopResult<OP, C>::type;
-  const int64_t n = rows * cols;
-  const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
-  for (int64_t i = (int64_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) {
-    int64_t r = i / cols, c = i - r * cols;
-    store_as<R>(out, odt, i,
-                bop_apply<OP>(load_as<C>(a, adt, r * ars + c * acs), load_as<C>(b, bdt, r * brs + c * bcs)));
+  // Each CTA walks bands of whole rows; inside a band the (row, col) split is a 32-bit division and four
+  // independent element loads are in flight per thread.
+  const int64_t band = cols >= (1 << 20) ? 1 : ((int64_t)EW_THREADS * EW_UNROLL * 4 + cols - 1) / cols;   // rows per band
+  const int64_t nbands = (rows + band - 1) / band;
+  const unsigned ucols = (unsigned)(cols < (1u << 31) ? cols : 1);
+  for (int64_t bb = blockIdx.x; bb < nbands; bb += gridDim.x) {
+    const int64_t r0 = bb * band;
+    const int64_t nr = (r0 + band < rows) ? band : rows - r0;
+    const int64_t cnt = nr * cols;
+    const int64_t obase = r0 * cols;
+    for (int64_t l0 = threadIdx.x; l0 < cnt; l0 += (int64_t)EW_THREADS * EW_UNROLL) {
+      C av[EW_UNROLL], bv[EW_UNROLL];
+#pragma unroll
+      for (int u = 0; u < EW_UNROLL; u++) {
+        int64_t l = l0 + (int64_t)u * EW_THREADS;
+        av[u] = C(); bv[u] = C();
+        if (l < cnt) {
+          int64_t r, c;
+          if (cols < (1u << 31) && cnt < (1u << 31)) { unsigned q = (unsigned)l / ucols; r = q; c = (unsigned)l - q * ucols; }
+          else { r = l / cols; c = l - r * cols; }
+          r += r0;
+          av[u] = load_as<C>(a, adt, r * ars + c * acs);
+          bv[u] = load_as<C>(b, bdt, r * brs + c * bcs);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < EW_UNROLL; u++) {
+        int64_t l = l0 + (int64_t)u * EW_THREADS;
+        if (l < cnt) store_as<R>(out, odt, obase + l, bop_apply<OP>(av[u], bv[u]));
+      }
+    }
   }
 }
 
@@ -295,7 +320,7 @@ static int launch_bop(int device, int ndim, const int64_t* shape, const void* a,
     s.sa[4 - ndim + i] = shape[i] == 1 ? 0 : sa[i];
     s.sb[4 - ndim + i] = shape[i] == 1 ? 0 : sb[i];
   }
-  int grid = grid_for(device, n, EW_THREADS, 1);
+  int grid = grid_for(device, n, EW_THREADS, s.shape[0] == 1 && s.shape[1] == 1 ? EW_UNROLL * 4 : 1);
   if (s.shape[0] == 1 && s.shape[1] == 1) {
     k_bop_2d<OP, C><<<grid, EW_THREADS, 0, st>>>(s.shape[2], s.shape[3], a, adt, s.sa[2], s.sa[3], b, bdt,
                                                 s.sb[2], s.sb[3], out, odt);

@@ -124,10 +124,18 @@ struct GlmRowsArgs {
   double* partials;    // [gridDim.x][2*d + 3]
 };
 
+// R rows per warp step.  NJ = 4 (d <= 256) runs 2 rows x 2 CTAs per SM rather than 4 x 1: the same bytes
+// in flight, but twice the warps to overlap the link's exp/log chain with the next loads.
+template <int NJ>
+struct RowsCfg {
+  static constexpr int R = NJ <= 2 ? 4 : (NJ <= 8 ? 2 : 1);
+  static constexpr int MIN_CTAS = NJ <= 4 ? 2 : 1;
+};
+
 template <int NJ, int WPR, bool VEC>
-__global__ void __launch_bounds__(GLM_THREADS)
+__global__ void __launch_bounds__(GLM_THREADS, RowsCfg<NJ>::MIN_CTAS)
 k_glm_rows(const GlmRowsArgs a) {
-  constexpr int R = NJ <= 4 ? 4 : (NJ == 8 ? 2 : 1);
+  constexpr int R = RowsCfg<NJ>::R;
   constexpr int NE = 2 * NJ;
   constexpr int NW = GLM_THREADS / 32;
   constexpr int RG = NW / WPR;
@@ -323,8 +331,8 @@ static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
 int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
-                    int ydt, const double* beta, const double* wext, bool link, double* stats, void* scratch,
-                    size_t scratch_bytes, cudaStream_t st);
+                    int ydt, const double* beta, const double* wext, bool link, double* stats, int64_t ldc,
+                    void* scratch, size_t scratch_bytes, cudaStream_t st);
 // 0: two passes, pass 2 = triangular DMMA kernel (default); 1: single fused pass; 2: two passes, pass 2 = generic GEMM
 static int glm_mode() {
   static int mode = -1;
@@ -395,7 +403,7 @@ static int launch_rows(int device, const GlmRowsArgs& a, int max_parts, int* npa
   int occ = 1;
   NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, GLM_THREADS, smem));
   if (occ < 1) occ = 1;
-  constexpr int R = NJ <= 4 ? 4 : (NJ == 8 ? 2 : 1);
+  constexpr int R = RowsCfg<NJ>::R;
   constexpr int RG = (GLM_THREADS / 32) / WPR;
   int64_t batches = (a.n + R - 1) / R;
   int64_t want = (batches + RG - 1) / RG;
@@ -458,7 +466,7 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   }
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);
   if (tri_ok && glm_mode() == 1)
-    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, nullptr, true, stats_d,
+    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, nullptr, true, stats_d, d + 1,
                            sc + L.off_gemm, L.total - L.off_gemm, st);
   GlmRowsArgs a;
   a.x = x_d; a.n = n; a.d = d; a.ldx = ldx; a.y = y_d; a.ydt = ydt; a.beta = beta_d;
@@ -475,7 +483,7 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   NB_LAUNCH_CHECK();
   if (tri_ok && glm_mode() == 0) {
     // pass 2: upper-triangular blocks of X^T diag(w) X by FP64 DMMA, mirrored -> exactly symmetric
-    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, false, stats_d,
+    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, false, stats_d, d + 1,
                            sc + L.off_gemm, L.total - L.off_gemm, st);
   }
   if (want_hess) {

@@ -66,6 +66,7 @@ struct FusedArgs {
   int C;                   // CTAs per group
   int groups;
   int64_t rows_per_group;  // multiple of FK
+  int64_t ldc;             // row stride of the output matrix (d + 1 inside the packed stats buffer)
   double* part_h;          // [groups][T][32*32]
   double* part_v;          // [groups][2*dp + 3]   g[dp] | u[dp] | sum r | sum w | objective
 };
@@ -382,7 +383,7 @@ k_tri_gram(const FusedArgs a) {
 // Sums the group partials in group order and assembles the packed [H | g | obj] buffer.
 __global__ void __launch_bounds__(256)
 k_fused_finish(const FusedArgs a, double* __restrict__ stats, int h_only) {
-  const int64_t d = a.d, p = d + 1;
+  const int64_t d = a.d, p = a.ldc;
   const int dp = a.nblk * FB;
   const int64_t nh = d * (d + 1) / 2;                // upper triangle of the d x d part
   const int64_t total = h_only ? nh : nh + 2 * d + 3;
@@ -501,14 +502,15 @@ static int run_fused(int device, const FusedArgs& a0, const FusedPlan& f, double
 // link == true : everything in one pass.
 // link == false: only the upper-triangular X^T diag(w) X (w = wext, null = ones) into the d x d corner of stats.
 int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
-                    int ydt, const double* beta, const double* wext, bool link, double* stats, void* scratch,
-                    size_t scratch_bytes, cudaStream_t st) {
+                    int ydt, const double* beta, const double* wext, bool link, double* stats, int64_t ldc,
+                    void* scratch, size_t scratch_bytes, cudaStream_t st) {
   FusedPlan f = plan_fused(device, n, d);
   NB_REQUIRE(scratch != nullptr && scratch_bytes >= f.scratch, "glm fused: scratch too small (%zu < %zu)",
              scratch_bytes, f.scratch);
   FusedArgs a;
   a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.wext = wext; a.family = family;
   a.nblk = f.nblk; a.T = f.T; a.C = f.C; a.groups = f.groups; a.rows_per_group = f.rows_per_group;
+  a.ldc = ldc;
   a.part_h = (double*)scratch;
   a.part_v = (double*)((char*)scratch + f.off_v);
   return link ? run_fused<true>(device, a, f, stats, st) : run_fused<false>(device, a, f, stats, st);

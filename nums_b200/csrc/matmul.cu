@@ -445,18 +445,24 @@ k_gemv_cols(int64_t m, int64_t k, int64_t chunk, int tile, const double* __restr
   double acc0 = 0.0, acc1 = 0.0;
   if (active && col < m) {
     int64_t kk = lo + tk;
-    for (; kk + kpar < hi; kk += 2 * kpar) {
+    double acc2 = 0.0, acc3 = 0.0;
+    for (; kk + 3 * (int64_t)kpar < hi; kk += 4 * kpar) {
       double v0 = a[kk * lda + col], v1 = a[(kk + kpar) * lda + col];
-      double x0 = x[kk * xs], x1 = x[(kk + kpar) * xs];
-      if (w) { x0 *= w[kk]; x1 *= w[kk + kpar]; }
+      double v2 = a[(kk + 2 * kpar) * lda + col], v3 = a[(kk + 3 * kpar) * lda + col];
+      double x0 = x[kk * xs], x1 = x[(kk + kpar) * xs], x2 = x[(kk + 2 * kpar) * xs], x3 = x[(kk + 3 * kpar) * xs];
+      if (w) { x0 *= w[kk]; x1 *= w[kk + kpar]; x2 *= w[kk + 2 * kpar]; x3 *= w[kk + 3 * kpar]; }
       acc0 = fma(v0, x0, acc0);
       acc1 = fma(v1, x1, acc1);
+      acc2 = fma(v2, x2, acc2);
+      acc3 = fma(v3, x3, acc3);
     }
-    if (kk < hi) {
+    for (; kk < hi; kk += kpar) {
       double x0 = x[kk * xs];
       if (w) x0 *= w[kk];
       acc0 = fma(a[kk * lda + col], x0, acc0);
     }
+    acc0 += acc2;
+    acc1 += acc3;
   }
   sm[t] = acc0 + acc1;
   __syncthreads();
@@ -596,6 +602,13 @@ k_matmul_i64_thread(int64_t m, int64_t n, int64_t k, const int64_t* __restrict__
 // ------------------------------------------------------------------------------------------------
 // dispatcher
 // ------------------------------------------------------------------------------------------------
+// glm_fused.cu: warp-specialised upper-triangular X^T diag(w) X for 8 <= d <= 256
+bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
+size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
+int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
+                    int ydt, const double* beta, const double* wext, bool link, double* stats, int64_t ldc,
+                    void* scratch, size_t scratch_bytes, cudaStream_t st);
+
 size_t gemm_scratch_bytes(int device, int64_t m, int64_t n, int64_t k) {
   if (m <= 0 || n <= 0 || k <= 0) return 0;
   size_t s = 0;
@@ -605,6 +618,7 @@ size_t gemm_scratch_bytes(int device, int64_t m, int64_t n, int64_t k) {
     size_t a = plan_gemm(device, m, n, k, false).scratch;
     size_t b = (m == n) ? plan_gemm(device, m, n, k, true).scratch : 0;
     s = a > b ? a : b;
+    if (m == n && n >= 8 && n <= 256) { size_t f = fused_scratch_bytes(device, k, n); if (f > s) s = f; }
   }
   return s;
 }
@@ -632,6 +646,9 @@ int gemm_f64(int device, int64_t m, int64_t n, int64_t k, const double* a, int64
   g.b = b; g.ldb = b_nc ? b_rs : b_cs;
   g.w = w; g.c = c; g.ldc = ldc;
   const bool sym = (a == b) && (m == n) && a_mc && b_nc && (a_cs == b_rs);
+  if (sym && fused_applicable(k, n, a_cs, a) && scratch != nullptr && scratch_bytes >= fused_scratch_bytes(device, k, n))
+    return glm_fused_stats(device, 0, a, k, n, a_cs, nullptr, NB_F64, nullptr, w, false, c, ldc, scratch,
+                           scratch_bytes, st);
   GemmPlan p = plan_gemm(device, m, n, k, sym);
   g.tiles_m = p.tiles_m; g.tiles_n = p.tiles_n; g.ntiles = p.ntiles; g.splits = p.splits; g.sym = p.sym;
   g.kchunk = p.kchunk;

@@ -154,18 +154,37 @@ k_reduce_rows(const void* __restrict__ a, int adt, int64_t outer, int64_t len, i
   }
 }
 
-// Kernel A2: inner == 1, short rows: one warp per row.
+// Kernel A2: inner == 1, short rows: LPR lanes per row (a power of two <= 32), 32/LPR rows per warp, so a
+// warp always covers >= 256 contiguous bytes per load instruction.
 template <int RED, typename T>
 __global__ void __launch_bounds__(RED_THREADS)
-k_reduce_rows_warp(const void* __restrict__ a, int adt, int64_t outer, int64_t len, void* __restrict__ out, int odt) {
+k_reduce_rows_warp(const void* __restrict__ a, int adt, int64_t outer, int64_t len, int lpr, void* __restrict__ out,
+                   int odt) {
   using R = Red<RED, T>;
+  using S = typename ShflT<T>::type;
   const int lane = threadIdx.x & 31;
+  const int rpw = 32 / lpr;                        // rows per warp
+  const int sub = lane / lpr, sl = lane % lpr;
   const int64_t warps = (int64_t)gridDim.x * (RED_THREADS / 32);
-  for (int64_t o = (int64_t)blockIdx.x * (RED_THREADS / 32) + (threadIdx.x >> 5); o < outer; o += warps) {
-    T acc = R::identity();
-    for (int64_t i = lane; i < len; i += 32) acc = R::combine(acc, R::pre(load_as<T>(a, adt, o * len + i)));
-    acc = warp_red<R, T>(acc);
-    if (lane == 0) store_as<T>(out, odt, o, acc);
+  for (int64_t o0 = ((int64_t)blockIdx.x * (RED_THREADS / 32) + (threadIdx.x >> 5)) * rpw; o0 < outer; o0 += warps * rpw) {
+    const int64_t o = o0 + sub;
+    T acc0 = R::identity(), acc1 = R::identity();
+    if (o < outer) {
+      const int64_t base = o * len;
+      int64_t i = sl;
+      for (; i + lpr < len; i += 2 * lpr) {
+        T v0 = load_as<T>(a, adt, base + i), v1 = load_as<T>(a, adt, base + i + lpr);
+        acc0 = R::combine(acc0, R::pre(v0));
+        acc1 = R::combine(acc1, R::pre(v1));
+      }
+      if (i < len) acc0 = R::combine(acc0, R::pre(load_as<T>(a, adt, base + i)));
+    }
+    T acc = R::combine(acc0, acc1);
+    for (int off = lpr >> 1; off > 0; off >>= 1) {
+      T other = (T)__shfl_down_sync(0xffffffffu, (S)acc, off);
+      acc = R::combine(acc, other);
+    }
+    if (sl == 0 && o < outer) store_as<T>(out, odt, o, acc);
   }
 }
 
@@ -206,13 +225,20 @@ k_reduce_cols(const void* __restrict__ a, int adt, int64_t outer, int64_t len, i
     if (active && col < inner) {
       const int64_t base = o * len * inner + col;
       int64_t k = lo + tk;
-      for (; k + kpar < hi; k += 2 * kpar) {
+      T acc2 = R::identity(), acc3 = R::identity();
+      for (; k + 3 * (int64_t)kpar < hi; k += 4 * kpar) {
         T v0 = load_as<T>(a, adt, base + k * inner);
         T v1 = load_as<T>(a, adt, base + (k + kpar) * inner);
+        T v2 = load_as<T>(a, adt, base + (k + 2 * kpar) * inner);
+        T v3 = load_as<T>(a, adt, base + (k + 3 * kpar) * inner);
         acc0 = R::combine(acc0, R::pre(v0));
         acc1 = R::combine(acc1, R::pre(v1));
+        acc2 = R::combine(acc2, R::pre(v2));
+        acc3 = R::combine(acc3, R::pre(v3));
       }
-      if (k < hi) acc0 = R::combine(acc0, R::pre(load_as<T>(a, adt, base + k * inner)));
+      for (; k < hi; k += kpar) acc0 = R::combine(acc0, R::pre(load_as<T>(a, adt, base + k * inner)));
+      acc0 = R::combine(acc0, acc2);
+      acc1 = R::combine(acc1, acc3);
     }
     __syncthreads();
     sm[t] = R::combine(acc0, acc1);
@@ -265,9 +291,11 @@ static int run_reduce(int device, int64_t outer, int64_t len, int64_t inner, con
     return 0;
   }
   if (inner == 1 && len <= 2048 && outer >= 64) {
-    int64_t blocks = (outer + 7) / 8;
+    int lpr = 32;
+    while (lpr > 1 && (int64_t)(lpr / 2) * 8 >= len) lpr >>= 1;      // ~8 elements per lane
+    int64_t blocks = (outer + 8 * (32 / lpr) - 1) / (8 * (32 / lpr));
     int grid = (int)(blocks < (int64_t)sms * 8 ? blocks : (int64_t)sms * 8);
-    k_reduce_rows_warp<RED, T><<<grid, RED_THREADS, 0, st>>>(a, adt, outer, len, out, odt);
+    k_reduce_rows_warp<RED, T><<<grid, RED_THREADS, 0, st>>>(a, adt, outer, len, lpr, out, odt);
     NB_LAUNCH_CHECK();
     return 0;
   }
@@ -487,6 +515,22 @@ constexpr int64_t WH_CHUNK = 8 * 32 * WH_STEPS;       // 4096 elements per chunk
 
 __device__ __forceinline__ void where_masks(const void* cond, int cdt, int64_t n, int64_t wbase, int lane,
                                             unsigned (&m)[WH_STEPS]) {
+  if (cdt == NB_BOOL && wbase + 32 * WH_STEPS <= n && ((((uintptr_t)cond) & 15) == 0)) {
+    // 1-byte conditions: one 16-byte load per lane covers the warp's 512 elements; the per-step ballots are
+    // rebuilt from the lanes' 16-bit masks (step j = lanes 2j and 2j+1)
+    const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(cond) + wbase + lane * 16);
+    const unsigned w[4] = {v.x, v.y, v.z, v.w};
+    unsigned mk = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+#pragma unroll
+      for (int b = 0; b < 4; b++)
+        if ((w[q] >> (8 * b)) & 0xffu) mk |= 1u << (4 * q + b);
+#pragma unroll
+    for (int j = 0; j < WH_STEPS; j++)
+      m[j] = __shfl_sync(0xffffffffu, mk, 2 * j) | (__shfl_sync(0xffffffffu, mk, 2 * j + 1) << 16);
+    return;
+  }
   bool f[WH_STEPS];
 #pragma unroll
   for (int j = 0; j < WH_STEPS; j++) {
