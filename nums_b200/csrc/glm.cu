@@ -128,7 +128,7 @@ struct GlmRowsArgs {
 // in flight, but twice the warps to overlap the link's exp/log chain with the next loads.
 template <int NJ>
 struct RowsCfg {
-  static constexpr int R = NJ <= 2 ? 4 : (NJ <= 8 ? 2 : 1);
+  static constexpr int R = NJ <= 4 ? 4 : (NJ <= 8 ? 2 : 1);
   static constexpr int MIN_CTAS = NJ <= 4 ? 2 : 1;
 };
 
@@ -156,8 +156,8 @@ k_glm_rows(const GlmRowsArgs a) {
   const int c0 = wc * CW + (VEC ? 2 * lane : lane);
 #define COL(e) (c0 + (VEC ? (64 * ((e) >> 1) + ((e) & 1)) : 32 * (e)))
 #define CV(e) ((int64_t)COL(e) < d)
-  double bet[NJ <= 4 ? NE : 1];
-  if constexpr (NJ <= 4) {
+  double bet[NJ <= 2 ? NE : 1];
+  if constexpr (NJ <= 2) {
 #pragma unroll
     for (int e = 0; e < NE; e++) bet[e] = CV(e) ? s_beta[COL(e)] : 0.0;
   }
@@ -202,7 +202,7 @@ k_glm_rows(const GlmRowsArgs a) {
 #pragma unroll
       for (int e = 0; e < NE; e++) {
         double bv;
-        if constexpr (NJ <= 4) bv = bet[e];
+        if constexpr (NJ <= 2) bv = bet[e];
         else bv = CV(e) ? s_beta[COL(e)] : 0.0;
         s = fma(xv[r][e], bv, s);
       }
@@ -333,6 +333,19 @@ size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
 int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
                     int ydt, const double* beta, const double* wext, bool link, double* stats, int64_t ldc,
                     void* scratch, size_t scratch_bytes, cudaStream_t st);
+// glm_rows_tma.cu
+bool rows_tma_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
+int glm_rows_tma(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                 const double* beta, int want_hess, double* wbuf, double* partials, int max_parts, int* nparts,
+                 cudaStream_t st);
+static int rows_mode() {     // 0 (default): register-resident k_glm_rows; 1: TMA-staged variant (experimental, slower)
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("NUMS_B200_ROWS_MODE");
+    mode = e ? atoi(e) : 0;
+  }
+  return mode;
+}
 // 0: two passes, pass 2 = triangular DMMA kernel (default); 1: single fused pass; 2: two passes, pass 2 = generic GEMM
 static int glm_mode() {
   static int mode = -1;
@@ -476,8 +489,12 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   a.partials = parts;
   int nparts = 0;
   const bool vec = ((ldx & 1) == 0) && ((((uintptr_t)x_d) & 15) == 0);
-  int rc = vec ? launch_rows_cfg<true>(device, a, L.max_parts, &nparts, st)
-               : launch_rows_cfg<false>(device, a, L.max_parts, &nparts, st);
+  int rc;
+  if (rows_mode() == 1 && rows_tma_applicable(n, d, ldx, x_d))
+    rc = glm_rows_tma(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, a.wbuf, parts, L.max_parts, &nparts, st);
+  else
+    rc = vec ? launch_rows_cfg<true>(device, a, L.max_parts, &nparts, st)
+             : launch_rows_cfg<false>(device, a, L.max_parts, &nparts, st);
   if (rc) return rc;
   k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 255) / 256), 256, 0, st>>>(d, nparts, parts, want_hess, stats_d);
   NB_LAUNCH_CHECK();

@@ -42,6 +42,25 @@ __device__ __forceinline__ double load_y(const void* y, int ydt, int64_t i) {
   return ydt == NB_F64 ? ((const double*)y)[i] : (double)((const int64_t*)y)[i];
 }
 
+// Newton needs only the residual and the weight: skips the objective's two logarithms.
+__device__ __forceinline__ LinkOut glm_link_noobj_rt(int family, double eta, double y) {
+  LinkOut o;
+  o.obj = 0.0;
+  if (family == NB_GLM_LOGISTIC) {
+    double mu = 1.0 / (1.0 + exp(-eta));
+    o.resid = mu - y;
+    o.wgt = mu * (1.0 - mu);
+  } else if (family == NB_GLM_POISSON) {
+    double mu = exp(eta);
+    o.resid = mu - y;
+    o.wgt = mu;
+  } else {
+    o.resid = eta - y;
+    o.wgt = 1.0;
+  }
+  return o;
+}
+
 __device__ __forceinline__ LinkOut glm_link_rt(int family, double eta, double y) {
   if (family == NB_GLM_LOGISTIC) return glm_link<NB_GLM_LOGISTIC>(eta, y);
   if (family == NB_GLM_POISSON) return glm_link<NB_GLM_POISSON>(eta, y);
