@@ -126,16 +126,19 @@ struct GlmRowsArgs {
 
 // R rows per warp step.  NJ = 4 (d <= 256) runs 2 rows x 2 CTAs per SM rather than 4 x 1: the same bytes
 // in flight, but twice the warps to overlap the link's exp/log chain with the next loads.
-template <int NJ>
+// Without the Hessian (L-BFGS / gradient passes) the u accumulators are not needed, which buys a second row
+// per step for the wide configurations: the link (~220 FP64 instructions, SIMT) is then paid once per 2-4
+// rows instead of once per row.
+template <int NJ, bool HESS>
 struct RowsCfg {
-  static constexpr int R = NJ <= 4 ? 4 : (NJ <= 8 ? 2 : 1);
+  static constexpr int R = NJ <= 4 ? 4 : (NJ <= 8 ? (HESS ? 2 : 4) : (HESS ? 1 : 2));
   static constexpr int MIN_CTAS = NJ <= 4 ? 2 : 1;
 };
 
-template <int NJ, int WPR, bool VEC>
-__global__ void __launch_bounds__(GLM_THREADS, RowsCfg<NJ>::MIN_CTAS)
+template <int NJ, int WPR, bool VEC, bool HESS>
+__global__ void __launch_bounds__(GLM_THREADS, RowsCfg<NJ, HESS>::MIN_CTAS)
 k_glm_rows(const GlmRowsArgs a) {
-  constexpr int R = RowsCfg<NJ>::R;
+  constexpr int R = RowsCfg<NJ, HESS>::R;
   constexpr int NE = 2 * NJ;
   constexpr int NW = GLM_THREADS / 32;
   constexpr int RG = NW / WPR;
@@ -163,9 +166,11 @@ k_glm_rows(const GlmRowsArgs a) {
   }
   const double beta0 = s_beta[d];
 
-  double g[NE], u[NE];
+  double g[NE], u[HESS ? NE : 1];
 #pragma unroll
-  for (int e = 0; e < NE; e++) { g[e] = 0.0; u[e] = 0.0; }
+  for (int e = 0; e < NE; e++) g[e] = 0.0;
+#pragma unroll
+  for (int e = 0; e < (HESS ? NE : 1); e++) u[e] = 0.0;
   double gi = 0.0, ui = 0.0, ob = 0.0;
 
   const int64_t nbatches = (n + R - 1) / R;
@@ -243,7 +248,7 @@ k_glm_rows(const GlmRowsArgs a) {
       const double rr = __shfl_sync(0xffffffffu, lo.resid, r);
 #pragma unroll
       for (int e = 0; e < NE; e++) g[e] = fma(rr, xv[r][e], g[e]);
-      if (a.want_hess) {
+      if constexpr (HESS) {
         const double ww = __shfl_sync(0xffffffffu, lo.wgt, r);
 #pragma unroll
         for (int e = 0; e < NE; e++) u[e] = fma(ww, xv[r][e], u[e]);
@@ -265,7 +270,7 @@ k_glm_rows(const GlmRowsArgs a) {
     if (rg == q) {
 #pragma unroll
       for (int e = 0; e < NE; e++) {
-        if (CV(e)) { s_g[COL(e)] += g[e]; s_u[COL(e)] += u[e]; }
+        if (CV(e)) { s_g[COL(e)] += g[e]; if constexpr (HESS) s_u[COL(e)] += u[e]; }
       }
       if (wc == 0 && lane == 0) { s_sc[0] += gi; s_sc[1] += ui; s_sc[2] += ob; }
     }
@@ -408,15 +413,15 @@ static int launch_small_d(int device, int64_t d, const double* x, int64_t n, int
   return 2;
 }
 
-template <int NJ, int WPR, bool VEC>
-static int launch_rows(int device, const GlmRowsArgs& a, int max_parts, int* nparts, cudaStream_t st) {
-  auto kern = k_glm_rows<NJ, WPR, VEC>;
+template <int NJ, int WPR, bool VEC, bool HESS>
+static int launch_rows_h(int device, const GlmRowsArgs& a, int max_parts, int* nparts, cudaStream_t st) {
+  auto kern = k_glm_rows<NJ, WPR, VEC, HESS>;
   size_t smem = ((size_t)((a.d + 2) & ~(int64_t)1) + 2 * (size_t)WPR * 64 * NJ + 4) * sizeof(double);
   NB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 1;
   NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, GLM_THREADS, smem));
   if (occ < 1) occ = 1;
-  constexpr int R = RowsCfg<NJ>::R;
+  constexpr int R = RowsCfg<NJ, HESS>::R;
   constexpr int RG = (GLM_THREADS / 32) / WPR;
   int64_t batches = (a.n + R - 1) / R;
   int64_t want = (batches + RG - 1) / RG;
@@ -428,6 +433,12 @@ static int launch_rows(int device, const GlmRowsArgs& a, int max_parts, int* npa
   NB_LAUNCH_CHECK();
   *nparts = (int)grid;
   return 0;
+}
+
+template <int NJ, int WPR, bool VEC>
+static int launch_rows(int device, const GlmRowsArgs& a, int max_parts, int* nparts, cudaStream_t st) {
+  return a.want_hess ? launch_rows_h<NJ, WPR, VEC, true>(device, a, max_parts, nparts, st)
+                     : launch_rows_h<NJ, WPR, VEC, false>(device, a, max_parts, nparts, st);
 }
 
 template <bool VEC>

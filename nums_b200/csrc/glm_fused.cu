@@ -69,10 +69,11 @@ struct FusedArgs {
   int nblk;                // ceil(d / 32)
   int T;                   // nblk (nblk + 1) / 2 upper-triangular blocks
   int C;                   // CTAs per group
+  int KG;                  // warps sharing one block (k-split inside the CTA) when there are few blocks
   int groups;
   int64_t rows_per_group;  // multiple of FK
   int64_t ldc;             // row stride of the output matrix (d + 1 inside the packed stats buffer)
-  double* part_h;          // [groups][T][32*32]
+  double* part_h;          // [groups * KG][T][32*32]
   double* part_v;          // [groups * C][2*dp + 3]   g[dp] | u[dp] | sum r | sum w | objective
 };
 
@@ -215,7 +216,9 @@ k_tri_gram(const FusedArgs a) {
   }
 
   // ---------------------------------------------------------------- consumers
-  const int t = c * W + warp;
+  const int bpc = W / a.KG;                        // blocks per CTA
+  const int kg = warp / bpc;                       // which k4-steps of a stage this warp takes
+  const int t = c * bpc + (warp % bpc);
   const bool has_block = t < a.T;
   int bi = 0, bj = 0;
   if (has_block) {
@@ -235,7 +238,7 @@ k_tri_gram(const FusedArgs a) {
     // the same "empty" phase
     mbar_wait(&fullx[slot], (unsigned)((kt / S) & 1));
     if constexpr (LINK) mbar_wait(&fullw[slot], (unsigned)((kt / S) & 1));
-    if (has_block) {
+    if (has_block && a.KG == 1) {
       const double* xs = sX + (size_t)slot * FK * ld;
       const double* ws = sWgt + slot * FK;
       const double* pa = xs + bi * FB + lq;
@@ -257,12 +260,29 @@ k_tri_gram(const FusedArgs a) {
 #pragma unroll
           for (int j = 0; j < 4; j++) f_dmma(acc[i][j][0], acc[i][j][1], af[cur][i], bf[cur][j]);
       }
+    } else if (has_block) {
+      // few blocks (small d): KG warps share a block, each taking every KG-th group of four rows
+      const double* xs = sX + (size_t)slot * FK * ld;
+      const double* ws = sWgt + slot * FK;
+      const double* pa = xs + bi * FB + lq;
+      const double* pb = xs + bj * FB + lq;
+      for (int ks = kg; ks < FK / 4; ks += a.KG) {
+        const int rr = ks * 4 + lr;
+        const double wv = ws[rr];
+        double af[4], bf[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { af[i] = pa[rr * ld + i * 8] * wv; bf[i] = pb[rr * ld + i * 8]; }
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int j = 0; j < 4; j++) f_dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+      }
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[slot]);     // this warp no longer reads the slot
   }
   if (has_block) {
-    double* p = a.part_h + ((size_t)group * a.T + t) * (FB * FB);
+    double* p = a.part_h + (((size_t)group * a.KG + kg) * a.T + t) * (FB * FB);
 #pragma unroll
     for (int i = 0; i < 4; i++)
 #pragma unroll
@@ -289,7 +309,7 @@ k_fused_finish(const FusedArgs a, double* __restrict__ stats, int h_only) {
       int t = bi * a.nblk - (bi * (bi - 1)) / 2 + (bj - bi);
       const double* src = a.part_h + (size_t)t * (FB * FB) + (i - bi * FB) * FB + (j - bj * FB);
       double s = 0.0;
-      for (int g = 0; g < a.groups; g++) s += src[(size_t)g * a.T * (FB * FB)];
+      for (int g = 0; g < a.groups * a.KG; g++) s += src[(size_t)g * a.T * (FB * FB)];
       stats[i * p + j] = s;
       stats[j * p + i] = s;
     } else {
@@ -309,14 +329,17 @@ k_fused_finish(const FusedArgs a, double* __restrict__ stats, int h_only) {
   }
 }
 
-struct FusedPlan { int W, S, nblk, T, C, groups; int64_t rows_per_group; size_t smem, scratch, off_v; };
+struct FusedPlan { int W, S, nblk, T, C, KG, groups; int64_t rows_per_group; size_t smem, scratch, off_v; };
 
 static FusedPlan plan_fused(int device, int64_t n, int64_t d, bool link) {
   FusedPlan f;
   f.nblk = (int)((d + FB - 1) / FB);
   f.T = f.nblk * (f.nblk + 1) / 2;
-  f.W = f.T <= 4 ? 4 : (f.T <= 8 ? 8 : 12);
-  f.C = (f.T + f.W - 1) / f.W;
+  // consumer warps W, of which KG share one block: T = 1 -> 4 warps x 1 block; 3 -> 12 warps, 4 per block;
+  // 6 -> 12 warps, 2 per block; >= 10 -> 12 warps, one block each over C CTAs
+  f.W = f.T == 1 ? 4 : 12;
+  f.KG = f.T == 1 ? 4 : (f.T == 3 ? 4 : (f.T == 6 ? 2 : 1));
+  f.C = (f.T + (f.W / f.KG) - 1) / (f.W / f.KG);
   const int sms = dev_info(device).sms;
   f.groups = sms / f.C;
   if (f.groups < 1) f.groups = 1;
@@ -332,7 +355,7 @@ static FusedPlan plan_fused(int device, int64_t n, int64_t d, bool link) {
   f.S = link ? 6 : 5;                               // single-pass mode keeps three stages with the aux warps
   while (f.S > 4 && (size_t)f.S * (stage + FK * 8) + fixed > (size_t)220 * 1024) f.S--;
   f.smem = (size_t)f.S * (stage + FK * 8) + fixed;
-  size_t ph = (size_t)f.groups * f.T * FB * FB * sizeof(double);
+  size_t ph = (size_t)f.groups * f.KG * f.T * FB * FB * sizeof(double);
   f.off_v = (ph + 255) & ~(size_t)255;
   f.scratch = f.off_v + (((size_t)f.groups * f.C * (2 * dp + 3) * sizeof(double) + 255) & ~(size_t)255);
   return f;
@@ -366,8 +389,7 @@ static int launch_tri(const FusedArgs& a, const FusedPlan& f, cudaStream_t st) {
 
 template <int S, bool LINK>
 static int launch_tri_w(const FusedArgs& a, const FusedPlan& f, cudaStream_t st) {
-  return f.W == 4 ? launch_tri<4, S, LINK>(a, f, st)
-                  : (f.W == 8 ? launch_tri<8, S, LINK>(a, f, st) : launch_tri<12, S, LINK>(a, f, st));
+  return f.W == 4 ? launch_tri<4, S, LINK>(a, f, st) : launch_tri<12, S, LINK>(a, f, st);
 }
 
 template <bool LINK>
@@ -395,7 +417,7 @@ int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t 
              scratch_bytes, f.scratch);
   FusedArgs a;
   a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.wext = wext; a.family = family;
-  a.nblk = f.nblk; a.T = f.T; a.C = f.C; a.groups = f.groups; a.rows_per_group = f.rows_per_group;
+  a.nblk = f.nblk; a.T = f.T; a.C = f.C; a.KG = f.KG; a.groups = f.groups; a.rows_per_group = f.rows_per_group;
   a.ldc = ldc;
   a.skip_obj = getenv("NUMS_B200_SKIP_OBJ") ? 1 : 0;
   a.part_h = (double*)scratch;

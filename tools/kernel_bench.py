@@ -121,6 +121,26 @@ def main():
         flops=2.0 * m ** 3)
     add("tensordot A^T@B 10^4 x 10^4", "BASELINE config 3", timeit(lambda: K.bop("tensordot", A, Bm, True, False, 1), reps=2, warm=1),
         flops=2.0 * m ** 3)
+    # GLM passes (the L-BFGS / gradient evaluation is pass 1 alone; Newton adds pass 2)
+    from nums_b200 import fused
+    del A, Bm, Xg
+    for dd in (64, 256, 1024):
+        nr = (n * 4) // dd if dd >= 256 else n // dd
+        Xd = big(nr * dd)
+        Xd = dv.DeviceBlock(Xd.t.view(nr, dd))
+        yd = dv.from_numpy((rng.random(1 << 20) < 0.5).astype(np.int64), 0)
+        yfull = dv.empty((nr,), np.int64, 0)
+        for lo in range(0, nr, yd.size):
+            hi = min(nr, lo + yd.size)
+            dv.copy_into(yfull.t[lo:hi], yd.t[: hi - lo])
+        bd = dv.from_numpy(rng.standard_normal(dd + 1) * 0.01, 0)
+        nbytes = nr * (8 * dd + 8)
+        for fam in ("logistic", "linear", "poisson") if dd == 1024 else ("logistic",):
+            add("glm_stats gradient+objective pass, %s, %d x %d (L-BFGS evaluation)" % (fam, nr, dd), "glms.py:457-489 / lbfgs.py:32-35",
+                timeit(lambda: fused.glm_stats(Xd, yfull, bd, fam, False), reps=3), nbytes)
+        add("glm_stats Newton pass (g + H), logistic, %d x %d" % (nr, dd), "glms.py:660-676",
+            timeit(lambda: fused.glm_stats(Xd, yfull, bd, "logistic", True), reps=3), nbytes, flops=nr * dd * (dd + 1))
+        del Xd, yfull
     S = rng.standard_normal((257, 257))
     S = dv.from_numpy(S.T @ S + np.eye(257), 0)
     add("inv 257 x 257", "numpy_kernel.py:471", timeit(lambda: K.inv(S), reps=5))
