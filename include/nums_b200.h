@@ -68,7 +68,8 @@ typedef enum {
 typedef enum {
   NB_GLM_LINEAR = 0,   /* LinearRegressionBase  glms.py:275-327 */
   NB_GLM_LOGISTIC = 1, /* LogisticRegression    glms.py:430-512 */
-  NB_GLM_POISSON = 2   /* PoissonRegression     glms.py:515-556 */
+  NB_GLM_POISSON = 2,  /* PoissonRegression     glms.py:515-556 */
+  NB_GLM_LOGISTIC_IRLS = 3 /* logistic with the IRLS weights mu(1-mu) + 1e-16, glms.py:679-700 */
 } nb_glm_family;
 
 /* ---- library ------------------------------------------------------------------------- */

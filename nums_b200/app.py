@@ -20,6 +20,10 @@ class NumsRandomState:
         self._km = km
         self._rng = km.get_rng(seed)
 
+    def numpy(self):
+        """A host Generator on the next block stream (random.py:32-36); used by sgd to pick rows."""
+        return cuda_kernel.block_rng(*self._rng.new_block_rng_params())
+
     def _sample(self, rfunc_name, shape, block_shape, dtype, rfunc_args):
         dtype = np.dtype(np.float64 if dtype is None else dtype)
         grid = ArrayGrid(shape, block_shape, dtype.name)

@@ -472,7 +472,7 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
                  int ydt, const double* beta_d, int want_hess, double* stats_d, void* scratch_d,
                  size_t scratch_bytes, void* stream) {
   NB_ENTER(device);
-  NB_REQUIRE(family >= NB_GLM_LINEAR && family <= NB_GLM_POISSON, "nb_glm_stats: unknown family %d", family);
+  NB_REQUIRE(family >= NB_GLM_LINEAR && family <= NB_GLM_LOGISTIC_IRLS, "nb_glm_stats: unknown family %d", family);
   NB_REQUIRE(d >= 1 && n >= 0 && ldx >= d, "nb_glm_stats: bad shape n=%lld d=%lld ldx=%lld", (long long)n,
              (long long)d, (long long)ldx);
   NB_REQUIRE(ydt == NB_F64 || ydt == NB_I64, "nb_glm_stats: y dtype %d not supported", ydt);
@@ -483,6 +483,7 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   double* parts = (double*)(sc + L.off_parts);
   if (d <= 7) {
     switch (family) {
+      case NB_GLM_LOGISTIC_IRLS: return launch_small_d<NB_GLM_LOGISTIC_IRLS>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
       case NB_GLM_LOGISTIC: return launch_small_d<NB_GLM_LOGISTIC>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
       case NB_GLM_POISSON: return launch_small_d<NB_GLM_POISSON>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
       default: return launch_small_d<NB_GLM_LINEAR>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);

@@ -9,11 +9,11 @@ struct LinkOut { double resid, wgt, obj; };
 template <int FAMILY>
 __device__ __forceinline__ LinkOut glm_link(double eta, double y) {
   LinkOut o;
-  if constexpr (FAMILY == NB_GLM_LOGISTIC) {
-    // glms.py:457-458 link_inv, :470 objective, :485 gradient residual, :495 hessian weights
+  if constexpr (FAMILY == NB_GLM_LOGISTIC || FAMILY == NB_GLM_LOGISTIC_IRLS) {
+    // glms.py:457-458 link_inv, :470 objective, :485 gradient residual, :495 hessian weights (:692 for irls)
     double mu = 1.0 / (1.0 + exp(-eta));
     o.resid = mu - y;
-    o.wgt = mu * (1.0 - mu);
+    o.wgt = mu * (1.0 - mu) + (FAMILY == NB_GLM_LOGISTIC_IRLS ? 1e-16 : 0.0);
     o.obj = -(y * log(mu) + (1.0 - y) * log(1.0 - mu));
   } else if constexpr (FAMILY == NB_GLM_POISSON) {
     // glms.py:516-517, :531, :544, :548
@@ -33,7 +33,7 @@ __device__ __forceinline__ LinkOut glm_link(double eta, double y) {
 
 template <int FAMILY>
 __device__ __forceinline__ double glm_mu(double eta) {
-  if constexpr (FAMILY == NB_GLM_LOGISTIC) return 1.0 / (1.0 + exp(-eta));
+  if constexpr (FAMILY == NB_GLM_LOGISTIC || FAMILY == NB_GLM_LOGISTIC_IRLS) return 1.0 / (1.0 + exp(-eta));
   else if constexpr (FAMILY == NB_GLM_POISSON) return exp(eta);
   else return eta;
 }
@@ -46,10 +46,10 @@ __device__ __forceinline__ double load_y(const void* y, int ydt, int64_t i) {
 __device__ __forceinline__ LinkOut glm_link_noobj_rt(int family, double eta, double y) {
   LinkOut o;
   o.obj = 0.0;
-  if (family == NB_GLM_LOGISTIC) {
+  if (family == NB_GLM_LOGISTIC || family == NB_GLM_LOGISTIC_IRLS) {
     double mu = 1.0 / (1.0 + exp(-eta));
     o.resid = mu - y;
-    o.wgt = mu * (1.0 - mu);
+    o.wgt = mu * (1.0 - mu) + (family == NB_GLM_LOGISTIC_IRLS ? 1e-16 : 0.0);
   } else if (family == NB_GLM_POISSON) {
     double mu = exp(eta);
     o.resid = mu - y;
@@ -63,6 +63,11 @@ __device__ __forceinline__ LinkOut glm_link_noobj_rt(int family, double eta, dou
 
 __device__ __forceinline__ LinkOut glm_link_rt(int family, double eta, double y) {
   if (family == NB_GLM_LOGISTIC) return glm_link<NB_GLM_LOGISTIC>(eta, y);
+  if (family == NB_GLM_LOGISTIC_IRLS) {       // irls(): s = mu * (1 - mu) + 1e-16 (glms.py:692)
+    LinkOut o = glm_link<NB_GLM_LOGISTIC>(eta, y);
+    o.wgt += 1e-16;
+    return o;
+  }
   if (family == NB_GLM_POISSON) return glm_link<NB_GLM_POISSON>(eta, y);
   return glm_link<NB_GLM_LINEAR>(eta, y);
 }

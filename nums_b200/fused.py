@@ -77,7 +77,21 @@ def stats_slice(stats, p, what):
     return DeviceBlock(t[p * p + p])
 
 
+def stats_add_g(stats, gvec):
+    """A copy of the packed stats whose gradient part has `gvec` added (blocks are immutable by convention)."""
+    from .cuda_kernel import KernelCls
+    dev = stats.device_index
+    gvec = dv.contiguous(dv.to_device(gvec, dev))
+    p = gvec.shape[0]
+    out = dv.empty(stats.shape, np.float64, dev)
+    dv.copy_into(out.t, stats.t)
+    summed = KernelCls().bop("add", DeviceBlock(stats.t[p * p: p * p + p]), gvec, False, False, {})
+    dv.copy_into(out.t[p * p: p * p + p], summed.t)
+    return out
+
+
 def register(km):
+    km.register("stats_add_g", stats_add_g, {})
     km.register("glm_stats", glm_stats, {})
     km.register("glm_newton_update", glm_newton_update, {})
     km.register("glm_predict", glm_predict, {})

@@ -48,6 +48,13 @@ class GLM:
             from .app import instance
             app = instance()
         self._app = app
+        if random_state is None:
+            self.rs = app.random
+        elif isinstance(random_state, (int, np.integer)):
+            from .app import NumsRandomState
+            self.rs = NumsRandomState(app.km, int(random_state))
+        else:
+            self.rs = random_state
         self._penalty = None if penalty == "none" else penalty
         if self._penalty not in (None, "l1", "l2", "elasticnet"):
             raise NotImplementedError("%s penalty not supported" % self._penalty)
@@ -100,6 +107,13 @@ class GLM:
             return LBFGS(self, m=10, max_iter=max_iter, thresh=tol).execute(X, y, beta)
         if self._opt == "gd":
             return gd(self, beta, X, y, tol, max_iter, self._lr)
+        if self._opt == "sgd":
+            return sgd(self, beta, X, y, tol, max_iter, self._lr)
+        if self._opt == "block_sgd":
+            return block_sgd(self, beta, X, y, tol, max_iter, self._lr)
+        if self._opt == "irls":
+            assert isinstance(self, LogisticRegression)
+            return irls(self, beta, X, y, tol, max_iter)
         raise Exception("Unsupported optimizer specified %s." % self._opt)
 
     def _setup_penalties(self, p, beta_block):
@@ -151,16 +165,17 @@ class GLM:
         dist.all_reduce(stats_oid.t, op=dist.ReduceOp.SUM)
         return stats_oid
 
-    def fused_stats(self, X, y, beta, want_hess):
+    def fused_stats(self, X, y, beta, want_hess, family=None):
         """Sum over all row blocks (and ranks) of the packed statistics at `beta` (single block)."""
         km = self._app.km
+        family = self.family if family is None else family
         b_oid = beta.blocks[(0,)].oid
         items = []
         for i in range(X.grid.grid_shape[0]):
             xb, yb = X.blocks[(i, 0)], y.blocks[(i,)]
             if xb.transposed:
                 raise NotImplementedError("fused path on a transposed X")
-            oid = km.call("glm_stats", xb.oid, yb.oid, b_oid, self.family, want_hess, syskwargs=xb.syskwargs())
+            oid = km.call("glm_stats", xb.oid, yb.oid, b_oid, family, want_hess, syskwargs=xb.syskwargs())
             items.append((oid, xb.grid_entry, xb.grid_shape, False))
         total = X.tree_reduce("sum", items, (0,), (1,))
         return self._allreduce(total)
@@ -330,6 +345,17 @@ class Ridge(LinearRegressionBase):
         super().__init__(penalty="l2", alpha=alpha, tol=tol, max_iter=max_iter, solver=solver, lr=lr, **kw)
 
 
+class ElasticNet(LinearRegressionBase):
+    def __init__(self, alpha=1.0, l1_ratio=0.5, tol=0.0001, max_iter=100, solver="newton", lr=0.01, **kw):
+        super().__init__(penalty="elasticnet", alpha=alpha, l1_ratio=l1_ratio, tol=tol, max_iter=max_iter,
+                         solver=solver, lr=lr, **kw)
+
+
+class Lasso(LinearRegressionBase):
+    def __init__(self, alpha=1.0, tol=0.0001, max_iter=100, solver="newton", lr=0.01, **kw):
+        super().__init__(penalty="l1", alpha=alpha, tol=tol, max_iter=max_iter, solver=solver, lr=lr, **kw)
+
+
 class LogisticRegression(GLM):
     family = "logistic"
 
@@ -367,6 +393,19 @@ class LogisticRegression(GLM):
 
     def predict(self, X):
         return (self.forward(X) > 0.5).astype(np.int64)
+
+    def predict_proba(self, X):
+        # glms.py:507-512: columns (P(y=1), P(y=0))
+        pos = self.forward(X).reshape((X.shape[0], 1), (X.block_shape[0], 1))
+        neg = 1 - pos
+        out = BlockArray(ArrayGrid((X.shape[0], 2), (X.block_shape[0], 2), "float64"), self._app.km)
+        for i in range(pos.grid.grid_shape[0]):
+            pb, nb = pos.blocks[(i, 0)], neg.blocks[(i, 0)]
+            out.blocks[(i, 0)].oid = self._app.km.create_block(
+                pb.oid, nb.oid, src_params=[((slice(None), slice(0, 1)), False), ((slice(None), slice(0, 1)), False)],
+                dst_params=[((slice(None), slice(0, 1)), False), ((slice(None), slice(1, 2)), False)],
+                dst_shape=(pb.shape[0], 2), dst_shape_bc=None, syskwargs=pb.syskwargs())
+        return out
 
 
 class PoissonRegression(GLM):
@@ -408,8 +447,6 @@ def newton(model, beta, X, y, tol, max_iter):
     km = app.km
     model.n_iter_ = 0
     if model._fused:
-        if model._penalty in ("l1", "elasticnet"):
-            raise NotImplementedError("fused Newton supports penalty none / l2; use fused=False")
         poisson_skip = isinstance(model, PoissonRegression)   # its gradient/hessian carry no penalty
         l2 = None
         if model._l2penalty_vec is not None and not poisson_skip:
@@ -418,6 +455,11 @@ def newton(model, beta, X, y, tol, max_iter):
         p = beta.shape[0]
         for _ in range(max_iter):
             stats = model.fused_stats(X, y, beta, True)
+            if model._l1penalty_vec is not None and not poisson_skip:
+                # the L1 term of grad_penalty (glms.py:254-264) is added to g before the update; its Hessian
+                # contribution is zero (:266-272)
+                extra = model._l1penalty_vec * app.map_uop("sign", beta)
+                stats = km.call("stats_add_g", stats, extra.blocks[(0,)].oid, syskwargs=sk)
             b_new, gmax, info = km.call("glm_newton_update", stats, l2, beta.blocks[(0,)].oid, syskwargs=sk)
             beta = BlockArray.from_oid(b_new, (p,), np.float64, km)
             model.n_iter_ += 1
@@ -451,6 +493,104 @@ def gd(model, beta, X, y, tol, max_iter, lr):
             mu = model.forward(X, beta)
             g = model.gradient(X, y, mu, beta=beta)
         beta = beta + (-lr_ba * g)
+        model.n_iter_ += 1
+        if app.max(app.abs(g)) <= tol_ba:
+            break
+    return beta
+
+
+def _row_range(arr, start, stop):
+    """Rows [start, stop) of a row-blocked array as an array whose blocks are windows on the owning blocks'
+    memory (the reference-copy case of view.py:104-128); the range must lie inside one row block."""
+    from .device import DeviceBlock
+    rb = arr.block_shape[0]
+    i = start // rb
+    if (stop - 1) // rb != i:
+        raise NotImplementedError("row ranges that straddle blocks")
+    lo, cnt = start - i * rb, stop - start
+    shape = (cnt,) + tuple(arr.shape[1:])
+    block_shape = (cnt,) + tuple(arr.block_shape[1:])
+    out = BlockArray(ArrayGrid(shape, block_shape, arr.grid.dtype), arr.km)
+    for entry in out.grid.get_entry_iterator():
+        src = arr.blocks[(i,) + tuple(entry[1:])]
+        if src.transposed:
+            raise NotImplementedError("row range of a transposed block")
+        out.blocks[entry].oid = DeviceBlock(src.oid.t[lo:lo + cnt])
+    return out
+
+
+def _gradient_any(model, X, y, beta):
+    if model._fused:
+        if _dist() is not None and model._sharded is not False:
+            raise NotImplementedError("sgd / block_sgd sample from the global array: not available row-sharded")
+        return model.objective_and_gradient(X, y, beta)[1]
+    return model.gradient(X, y, model.forward(X, beta), beta=beta)
+
+
+def sgd(model, beta, X, y, tol, max_iter, lr):
+    """glms.py:595-616: one uniformly drawn row per step (host RNG: model.rs.numpy().integers)."""
+    app = model._app
+    tol_ba, lr_ba = app.scalar(tol), app.scalar(lr)
+    model.n_iter_ = 0
+    for _ in range(max_iter):
+        idx = int(model.rs.numpy().integers(X.shape[0]))
+        g = _gradient_any(model, _row_range(X, idx, idx + 1), _row_range(y, idx, idx + 1), beta)
+        beta = beta + (-lr_ba * g)
+        model.n_iter_ += 1
+        if app.max(app.abs(g)) <= tol_ba:
+            break
+    return beta
+
+
+def block_sgd(model, beta, X, y, tol, max_iter, lr):
+    """glms.py:619-639: one step per row block; the convergence test only leaves the inner loop (as in the
+    reference)."""
+    app = model._app
+    tol_ba, lr_ba = app.scalar(tol), app.scalar(lr)
+    model.n_iter_ = 0
+    rb = X.block_shape[0]
+    for _ in range(max_iter):
+        for start in range(0, X.shape[0], rb):
+            stop = min(X.shape[0], start + rb)
+            g = _gradient_any(model, _row_range(X, start, stop), _row_range(y, start, stop), beta)
+            beta = beta + (-lr_ba * g)
+            if app.max(app.abs(g)) <= tol_ba:
+                break
+        model.n_iter_ += 1
+    return beta
+
+
+def irls(model, beta, X, y, tol, max_iter):
+    """glms.py:679-700.  Fused: H' = X^T diag(mu(1-mu)+1e-16) X and g0 = X^T(mu - y) from one statistics
+    pass; X^T S z = H' beta - g0 because z = eta + (y - mu)/s and eta = X beta."""
+    app = model._app
+    km = app.km
+    model.n_iter_ = 0
+    tol_ba = app.scalar(tol)
+    if not model._fused:
+        for _ in range(max_iter):
+            eta = X @ beta
+            mu = model.link_inv(eta)
+            s = mu * (1 - mu) + 1e-16
+            XT_s = X.transpose(defer=True) * s
+            XTsX_inv = inv(app, XT_s @ X)
+            z = eta + (y - mu) / s
+            beta = XTsX_inv @ XT_s @ z
+            g = model.gradient(X, y, mu, beta)
+            model.n_iter_ += 1
+            if app.max(app.abs(g)) <= tol_ba:
+                break
+        return beta
+    p = beta.shape[0]
+    sk = {"grid_entry": (0,), "grid_shape": (1,)}
+    for _ in range(max_iter):
+        stats = model.fused_stats(X, y, beta, True, family="logistic_irls")
+        H = BlockArray.from_oid(km.call("stats_slice", stats, p, "H", syskwargs={"grid_entry": (0, 0), "grid_shape": (1, 1)}),
+                                (p, p), np.float64, km)
+        g0 = BlockArray.from_oid(km.call("stats_slice", stats, p, "g", syskwargs=sk), (p,), np.float64, km)
+        new_beta = inv(app, H) @ (H @ beta - g0)
+        g = g0 if model._penalty is None else g0 + model.grad_penalty(new_beta)    # :698 uses the NEW beta
+        beta = new_beta
         model.n_iter_ += 1
         if app.max(app.abs(g)) <= tol_ba:
             break

@@ -54,7 +54,7 @@ _RED_NAMES = ["sum", "prod", "min", "max", "all", "any", "nansum", "nanmin", "na
 RED_CODE = {name: i for i, name in enumerate(_RED_NAMES)}
 RED_ALIAS = {"amin": "min", "amax": "max", "alltrue": "all", "sometrue": "any", "product": "prod"}
 
-FAMILY_CODE = {"linear": 0, "logistic": 1, "poisson": 2}
+FAMILY_CODE = {"linear": 0, "logistic": 1, "poisson": 2, "logistic_irls": 3}
 
 
 def dtype_code(dtype):

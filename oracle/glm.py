@@ -185,6 +185,71 @@ def gd(model, tol=1e-4, max_iter=100, lr=0.01):
     return beta, it
 
 
+def sgd(model, X, y, tol=1e-4, max_iter=100, lr=0.01, seed=None):
+    """glms.py:595-616; the row index comes from model.rs.numpy().integers(n): a fresh block generator per
+    step (random.py:32-36), i.e. PCG64(seed).jumped(step)."""
+    from .np_kernel import block_rng
+    beta = np.zeros(model.p)
+    n = X.shape[0]
+    it = 0
+    for step in range(max_iter):
+        idx = int(block_rng(seed, step).integers(n))
+        one = BlockedGLM(model.fam.name, [X[idx:idx + 1].astype(float)], [y[idx:idx + 1]], model.penalty, 1.0)
+        one.l1vec, one.l2vec, one.l1, one.l2 = model.l1vec, model.l2vec, model.l1, model.l2
+        g = one.gradient(beta)
+        beta = beta + (-lr * g)
+        it += 1
+        if np.max(np.abs(g)) <= tol:
+            break
+    return beta, it
+
+
+def block_sgd(model, tol=1e-4, max_iter=100, lr=0.01):
+    """glms.py:619-639 (the convergence test leaves only the inner loop)."""
+    beta = np.zeros(model.p)
+    it = 0
+    for _ in range(max_iter):
+        for xb, yb in zip(model.Xb, model.yb):
+            one = BlockedGLM(model.fam.name, [xb], [yb], model.penalty, 1.0)
+            one.l1vec, one.l2vec, one.l1, one.l2 = model.l1vec, model.l2vec, model.l1, model.l2
+            g = one.gradient(beta)
+            beta = beta + (-lr * g)
+            if np.max(np.abs(g)) <= tol:
+                break
+        it += 1
+    return beta, it
+
+
+def irls(model, tol=1e-4, max_iter=100):
+    """glms.py:679-700 (logistic only), on the blocked arrays incl. the p x n temporaries it builds."""
+    beta = np.zeros(model.p)
+    d = model.d
+    it = 0
+    for _ in range(max_iter):
+        etas, mus = model.forward(beta)
+        h00, h01, h10, h11, t0, t1 = [], [], [], [], [], []
+        for xb, ob, eta, mu, yb in zip(model.Xb, model.ones, etas, mus, model.yb):
+            s = mu * (1 - mu) + 1e-16
+            xs, os_ = xb.T * s, ob.T * s                  # X.T(defer) * s, per column block
+            z = eta + (yb - mu) / s
+            h00.append(np.matmul(xs, xb)); h01.append(np.matmul(xs, ob))
+            h10.append(np.matmul(os_, xb)); h11.append(np.matmul(os_, ob))
+            t0.append((xs, z)); t1.append((os_, z))
+        H = np.block([[tree_sum(h00), tree_sum(h01)], [tree_sum(h10), tree_sum(h11)]])
+        Hinv = np.linalg.inv(H)
+        # (XTsX_inv @ XT_s) @ z with XT_s blocked (2 x R): form the (p x rb) products per row block first
+        acc = []
+        for (xs, z), (os_, _) in zip(t0, t1):
+            m_top = np.matmul(Hinv[:, :d], xs) + np.matmul(Hinv[:, d:], os_)      # (p, rb)
+            acc.append(np.matmul(m_top, z))
+        beta = tree_sum(acc)
+        g = model.gradient(beta, (etas, mus))
+        it += 1
+        if np.max(np.abs(g)) <= tol:
+            break
+    return beta, it
+
+
 def lbfgs(model, tol=1e-4, max_iter=100, m=10):
     """lbfgs.py:102-159 with its line search :37-52 and memory :55-62."""
     theta = np.zeros(model.p)
@@ -247,15 +312,21 @@ def lbfgs(model, tol=1e-4, max_iter=100, m=10):
 
 
 def fit(family, X, y, row_block, solver="newton", penalty=None, lam=1.0, tol=1e-4, max_iter=100, lr=0.01,
-        trace=None):
+        trace=None, l1_ratio=0.5, seed=None):
     """GLM.fit (glms.py:115-192) on host arrays cut into row blocks of `row_block` rows."""
     if np.issubdtype(X.dtype, np.integer):
         X = X.astype(float)
-    model = BlockedGLM(family, split_rows(X, row_block), split_rows(y, row_block), penalty, lam)
+    model = BlockedGLM(family, split_rows(X, row_block), split_rows(y, row_block), penalty, lam, l1_ratio)
+    if solver == "sgd":
+        return sgd(model, X, y, tol, max_iter, lr, seed)
     if solver in ("newton", "newton-cg"):
         return newton(model, tol, max_iter, trace)
     if solver == "lbfgs":
         return lbfgs(model, tol, max_iter)
     if solver == "gd":
         return gd(model, tol, max_iter, lr)
+    if solver == "block_sgd":
+        return block_sgd(model, tol, max_iter, lr)
+    if solver == "irls":
+        return irls(model, tol, max_iter)
     raise ValueError(solver)

@@ -122,6 +122,34 @@ def main():
     out["stats_obj"] = m.objective(Xa, yb, beta, mu).get()
     save("glm_logistic_d32", **out)
 
+    # ---------------------------------------------------------------- the other solvers / penalties
+    from nums.models.glms import Lasso, ElasticNet
+    out = {}
+    for tag, cls, kw in [
+        ("irls", LogisticRegression, dict(solver="irls", penalty="none", max_iter=4)),
+        ("irls_l2", LogisticRegression, dict(solver="irls", penalty="l2", C=2.0, max_iter=4)),
+        ("block_sgd", LogisticRegression, dict(solver="block_sgd", penalty="l2", C=2.0, max_iter=3, lr=1e-4)),
+        ("sgd", LogisticRegression, dict(solver="sgd", penalty="l2", C=2.0, max_iter=25, lr=1e-2, random_state=7)),
+        ("newton_l1", LogisticRegression, dict(solver="newton", penalty="l1", C=5.0, max_iter=4)),
+        ("newton_en", LogisticRegression, dict(solver="newton", penalty="elasticnet", C=5.0, max_iter=4)),
+    ]:
+        m = cls(**kw)
+        m.fit(Xb, yb)
+        out[tag + "_beta"] = m._beta.get()
+        out[tag + "_beta0"] = m._beta0.get()
+    m = LogisticRegression(solver="newton", penalty="l2", C=2.0, max_iter=6)
+    m.fit(Xb, yb)
+    out["proba"] = m.predict_proba(Xb).get()
+    y_lin32 = Xh @ w_true + 0.1 * np.cos(np.arange(n))
+    for tag, cls, kw in [("lasso", Lasso, dict(alpha=0.3, solver="newton", max_iter=3)),
+                         ("enet", ElasticNet, dict(alpha=0.3, l1_ratio=0.4, solver="newton", max_iter=3))]:
+        m = cls(**kw)
+        m.fit(Xb, app.array(y_lin32, block_shape=(rb,)))
+        out[tag + "_beta"] = m._beta.get()
+        out[tag + "_beta0"] = m._beta0.get()
+    out["y_lin32"] = y_lin32
+    save("glm_solvers_d32", **out)
+
     # ---------------------------------------------------------------- linear / ridge / poisson, d=8
     n, d, rb = 3000, 8, 1000
     Xb = rs.normal(shape=(n, d), block_shape=(rb, d))

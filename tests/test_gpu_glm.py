@@ -282,3 +282,37 @@ def test_full_size_glm_pass_properties(app):
     assert np.array_equal(H, H.T)
     assert rel_err(a + b, full) < STAT_TOL
     assert np.all(np.linalg.eigvalsh(H) > 0)
+
+
+# ------------------------------------------------------------------------------------------------
+# the other solvers / penalties, against the reference's golden coefficients
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("tag,kw", [
+    ("irls", dict(solver="irls", penalty="none", max_iter=4)),
+    ("irls_l2", dict(solver="irls", penalty="l2", C=2.0, max_iter=4)),
+    ("block_sgd", dict(solver="block_sgd", penalty="l2", C=2.0, max_iter=3, lr=1e-4)),
+    ("sgd", dict(solver="sgd", penalty="l2", C=2.0, max_iter=25, lr=1e-2, random_state=7)),
+    ("newton_l1", dict(solver="newton", penalty="l1", C=5.0, max_iter=4)),
+    ("newton_en", dict(solver="newton", penalty="elasticnet", C=5.0, max_iter=4)),
+])
+def test_other_solvers_d32(app, fused, tag, kw):
+    from nums_b200.glms import LogisticRegression
+    g, s = load_golden("glm_logistic_d32"), load_golden("glm_solvers_d32")
+    m, _, _ = fit_dev(app, LogisticRegression, g["X"], g["y"], int(g["row_block"]), fused=fused, **kw)
+    coef_close(m, s[tag + "_beta"], s[tag + "_beta0"])
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_lasso_elasticnet_and_proba(app, fused):
+    from nums_b200.glms import ElasticNet, Lasso, LogisticRegression
+    g, s = load_golden("glm_logistic_d32"), load_golden("glm_solvers_d32")
+    rb = int(g["row_block"])
+    m, _, _ = fit_dev(app, Lasso, g["X"], s["y_lin32"], rb, fused=fused, alpha=0.3, solver="newton", max_iter=3)
+    coef_close(m, s["lasso_beta"], s["lasso_beta0"])
+    m, _, _ = fit_dev(app, ElasticNet, g["X"], s["y_lin32"], rb, fused=fused, alpha=0.3, l1_ratio=0.4, solver="newton",
+                      max_iter=3)
+    coef_close(m, s["enet_beta"], s["enet_beta0"])
+    m, Xb, _ = fit_dev(app, LogisticRegression, g["X"], g["y"], rb, fused=fused, solver="newton", penalty="l2", C=2.0,
+                       max_iter=6)
+    assert rel_err(m.predict_proba(Xb).get(), s["proba"]) < STAT_TOL

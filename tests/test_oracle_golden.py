@@ -104,3 +104,26 @@ def test_blockarray_level():
         red = ok.arg_op("argmax", b, slice(i * rb, (i + 1) * rb), *red)
     assert red[0] == g["argmax_p"]
     assert oglm.tree_sum([np.sum(b) for b in pb]) == g["sum_p"]
+
+
+@pytest.mark.parametrize("tag,kw", [
+    ("irls", dict(solver="irls", penalty=None, max_iter=4)),
+    ("irls_l2", dict(solver="irls", penalty="l2", lam=0.5, max_iter=4)),
+    ("block_sgd", dict(solver="block_sgd", penalty="l2", lam=0.5, max_iter=3, lr=1e-4)),
+    ("sgd", dict(solver="sgd", penalty="l2", lam=0.5, max_iter=25, lr=1e-2, seed=7)),
+    ("newton_l1", dict(solver="newton", penalty="l1", lam=0.2, max_iter=4)),
+    ("newton_en", dict(solver="newton", penalty="elasticnet", lam=0.2, max_iter=4)),
+])
+def test_other_solvers_d32(tag, kw):
+    g, s = load_golden("glm_logistic_d32"), load_golden("glm_solvers_d32")
+    beta, _ = oglm.fit("logistic", g["X"], g["y"], int(g["row_block"]), **kw)
+    assert rel_err(beta[:-1], s[tag + "_beta"]) < 1e-9
+    assert abs(beta[-1] - s[tag + "_beta0"]) < 1e-9 * max(1.0, abs(s[tag + "_beta0"]))
+
+
+@pytest.mark.parametrize("tag,kw", [("lasso", dict(penalty="l1", lam=0.3, max_iter=3)),
+                                    ("enet", dict(penalty="elasticnet", lam=0.3, l1_ratio=0.4, max_iter=3))])
+def test_lasso_elasticnet_d32(tag, kw):
+    g, s = load_golden("glm_logistic_d32"), load_golden("glm_solvers_d32")
+    beta, _ = oglm.fit("linear", g["X"], s["y_lin32"], int(g["row_block"]), solver="newton", **kw)
+    assert rel_err(beta[:-1], s[tag + "_beta"]) < 1e-9
