@@ -145,6 +145,27 @@ def main():
     S = dv.from_numpy(S.T @ S + np.eye(257), 0)
     add("inv 257 x 257", "numpy_kernel.py:471", timeit(lambda: K.inv(S), reps=5))
 
+    # BASELINE config 1: the README fit (10^6 x 2, newton-cg, l2, C=10), wall clock incl. host control flow
+    import time
+    import warnings
+    from nums_b200.glms import LogisticRegression
+    half = 500_000
+    r2 = np.random.default_rng(1337)
+    X1 = np.concatenate([r2.standard_normal((half, 2)), r2.standard_normal((half, 2)) + 2.0])
+    y1 = np.concatenate([np.zeros(half, dtype=np.int64), np.ones(half, dtype=np.int64)])
+    Xb1, yb1 = app.array(X1, block_shape=(half, 2)), app.array(y1, block_shape=(half,))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for _ in range(2):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            m1 = LogisticRegression(app=app, solver="newton-cg", penalty="l2", C=10)
+            m1.fit(Xb1, yb1)
+            b1 = m1._beta.get()
+            dt1 = time.perf_counter() - t0
+    rows.append({"kernel": "README fit: LogisticRegression newton-cg 10^6 x 2, %d iterations, beta=%s (wall clock)"
+                           % (m1.n_iter_, np.round(b1, 4).tolist()), "reference": "README.md:115-130", "ms": dt1 * 1e3})
+
     lines = ["| kernel | reference | ms | GB/s | of HBM peak (%.0f GB/s measured) | TFLOP/s | of FP64 DMMA peak |" % hbm,
              "|---|---|---:|---:|---:|---:|---:|"]
     for r in rows:
