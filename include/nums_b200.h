@@ -135,6 +135,14 @@ int nb_copy_strided(int device, int ndim, const int64_t* shape, int itemsize,
                     const void* src_d, const int64_t* sstrides,
                     void* dst_d, const int64_t* dstrides, void* stream);
 
+/* ---- KernelCls.random_block for rfunc "random" (numpy_kernel.py:103-110, block_rng :31-32) ----------- */
+
+/* n uniform doubles in [0,1), bit-identical to Generator(PCG64(seed).jumped(j)).random(n): the host passes
+ * that bit generator's 128-bit state and increment as {hi, lo} pairs (seeding/jumping stay in NumPy);
+ * the device advances each thread to its position with the O(log k) LCG jump. */
+int nb_pcg64_random(int device, int64_t n, const uint64_t* state_hi_lo, const uint64_t* inc_hi_lo,
+                    double* out_d, void* stream);
+
 /* ---- reductions: KernelCls.reduce_axis :294-313, sum_reduce :291, bop_reduce :433-453 -- */
 
 /* Views the input as [outer, len, inner] (C order) and reduces the middle axis:

@@ -100,13 +100,28 @@ class KernelCls:
         return out
 
     def random_block(self, rng_params, rfunc_name, rfunc_args, shape, dtype, device_index=None):
-        # numpy_kernel.py:103-110.  Inputs are generated by the reference's own host RNG stream
-        # (bit-identical to the NumPy backend) and uploaded; see DESIGN.md "inputs".
+        # numpy_kernel.py:103-110.  Uniform doubles are generated on the device, bit-identical to the host
+        # stream; every other distribution is drawn by the reference's own host RNG and uploaded (ziggurat /
+        # rejection samplers consume a data-dependent number of draws); see DESIGN.md "inputs".
+        if rfunc_name == "random" and len(rfunc_args) == 1 and np.dtype(dtype) == np.dtype(np.float64):
+            return self._random_on_device(rng_params, int(rfunc_args[0]), shape, _cur(device_index))
         rng = block_rng(*rng_params)
         result = getattr(rng, rfunc_name)(*rfunc_args).reshape(shape)
         if rfunc_name not in ("random", "integers"):
             result = result.astype(dtype)
         return dv.from_numpy(result, _cur(device_index))
+
+    def _random_on_device(self, rng_params, size, shape, dev):
+        """Uniform doubles generated in HBM, bit-identical to the host stream: NumPy seeds and jumps the
+        bit generator, the device produces the values (nb_pcg64_random)."""
+        seed, jump = rng_params
+        st = PCG64(seed).jumped(jump).state["state"]
+        mask = (1 << 64) - 1
+        state = (C.c_uint64 * 2)(st["state"] >> 64, st["state"] & mask)
+        inc = (C.c_uint64 * 2)(st["inc"] >> 64, st["inc"] & mask)
+        out = dv.empty((size,), np.float64, dev)
+        _lib.check(_lib.load().nb_pcg64_random(dev, size, state, inc, out.ptr, dv.stream_ptr(dev)))
+        return DeviceBlock(out.t.view(tuple(shape)))
 
     def permutation(self, rng_params, size, device_index=None):
         # numpy_kernel.py:112-114

@@ -306,3 +306,17 @@ def test_plumbing_blocks(K):
     np.testing.assert_array_equal(down(Ad), A)      # inputs are never mutated (numpy_kernel.py:131-135)
     ident = K.new_block("eye", (0, 0), {"shape": (6, 6), "block_shape": (6, 6), "dtype": "float64"}, device_index=0)
     np.testing.assert_array_equal(down(ident), np.eye(6))
+
+
+@pytest.mark.parametrize("n,jump", [(1, 0), (1000, 3), (1_000_003, 5), (10_000_000, 17)])
+def test_device_block_rng_uniform_is_bit_identical(K, n, jump):
+    """random_block("random") is generated in HBM and must equal the reference's host stream
+    Generator(PCG64(seed).jumped(jump)).random(n) bit for bit (numpy_kernel.py:31-32,103-110)."""
+    got = down(K.random_block((1337, jump), "random", (n,), (n,), np.float64, device_index=0))
+    want = ok.random_block((1337, jump), "random", (n,), (n,), np.float64)
+    np.testing.assert_array_equal(got, want)
+    mat = down(K.random_block((42, jump), "random", (6 * 7,), (6, 7), np.float64, device_index=0))
+    np.testing.assert_array_equal(mat, ok.random_block((42, jump), "random", (6 * 7,), (6, 7), np.float64))
+    # other distributions still come from the host stream, unchanged
+    z = down(K.random_block((1337, jump), "normal", (0.0, 1.0, 257), (257,), np.float64, device_index=0))
+    np.testing.assert_array_equal(z, ok.random_block((1337, jump), "normal", (0.0, 1.0, 257), (257,), np.float64))
