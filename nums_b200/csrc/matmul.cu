@@ -8,6 +8,7 @@
 // the whole grid; partial tiles go to caller-provided scratch and are summed in a fixed order
 // (deterministic, no atomics).  Matrix.vector / dot are HBM-bound streaming kernels.
 #include "gemm.cuh"
+#include <stdlib.h>
 
 namespace nb {
 
@@ -602,6 +603,11 @@ k_matmul_i64_thread(int64_t m, int64_t n, int64_t k, const int64_t* __restrict__
 // ------------------------------------------------------------------------------------------------
 // dispatcher
 // ------------------------------------------------------------------------------------------------
+// matmul_ws.cu: warp-specialised, TMA-fed kernel for large m, n
+bool gemm_ws_applicable(int device, int64_t m, int64_t n, int64_t k, const double* a, int64_t lda, const double* b,
+                        int64_t ldb, const double* c, int64_t ldc);
+int gemm_ws_f64(int64_t m, int64_t n, int64_t k, const double* a, int64_t lda, bool a_mc, const double* b, int64_t ldb,
+                bool b_nc, double* c, int64_t ldc, cudaStream_t st);
 // glm_fused.cu: warp-specialised upper-triangular X^T diag(w) X for 8 <= d <= 256
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
@@ -649,6 +655,8 @@ int gemm_f64(int device, int64_t m, int64_t n, int64_t k, const double* a, int64
   if (sym && fused_applicable(k, n, a_cs, a) && scratch != nullptr && scratch_bytes >= fused_scratch_bytes(device, k, n))
     return glm_fused_stats(device, 0, a, k, n, a_cs, nullptr, NB_F64, nullptr, w, false, c, ldc, scratch,
                            scratch_bytes, st);
+  if (w == nullptr && !getenv("NUMS_B200_NO_WS") && gemm_ws_applicable(device, m, n, k, a, g.lda, b, g.ldb, c, ldc))
+    return gemm_ws_f64(m, n, k, a, g.lda, a_mc, b, g.ldb, b_nc, c, ldc, st);
   GemmPlan p = plan_gemm(device, m, n, k, sym);
   g.tiles_m = p.tiles_m; g.tiles_n = p.tiles_n; g.ntiles = p.ntiles; g.splits = p.splits; g.sym = p.sym;
   g.kchunk = p.kchunk;

@@ -320,3 +320,16 @@ def test_device_block_rng_uniform_is_bit_identical(K, n, jump):
     # other distributions still come from the host stream, unchanged
     z = down(K.random_block((1337, jump), "normal", (0.0, 1.0, 257), (257,), np.float64, device_index=0))
     np.testing.assert_array_equal(z, ok.random_block((1337, jump), "normal", (0.0, 1.0, 257), (257,), np.float64))
+
+
+@pytest.mark.parametrize("m,n,k", [(1664, 1664, 512), (1666, 1730, 1002), (2048, 1540, 70)])
+@pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
+def test_matmul_large_tma_path(K, m, n, k, ta, tb):
+    """Sizes that fill the machine with 128x128 tiles take the warp-specialised TMA-fed kernel (matmul_ws.cu),
+    including ragged m / n / k tails."""
+    rng = np.random.default_rng(m + n + k)
+    A = rng.standard_normal((k, m) if ta else (m, k))
+    B = rng.standard_normal((n, k) if tb else (k, n))
+    got = down(K.bop("tensordot", up(A), up(B), ta, tb, 1))
+    want = ok.bop("tensordot", A, B, ta, tb, 1)
+    assert rel_err(got, want) < FTOL
