@@ -98,7 +98,7 @@ def cpu_newton_steps(rows, d, steps, warmup=1):
     return algorithmic_bytes(rows, d) / dt / 1e9, dt, cores
 
 
-def run_reference(args):
+def run_reference(args, result):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -116,7 +116,7 @@ def run_reference(args):
         "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    result["line"] = line
     return 0
 
 
@@ -167,7 +167,7 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
-def run_ours(args):
+def run_ours(args, result):
     import torch
     import torch.distributed as dist
     from nums_b200 import _lib, device as dv, fused
@@ -384,17 +384,38 @@ def run_ours(args):
             "sample": "%d x %d rows (4 row blocks), %d Newton iterations of the reference algorithm "
                       "(oracle/glm.py), NumPy/OpenBLAS on %d threads, %.2f s/iteration"
                       % (args.cpu_rows, d, args.cpu_steps, cores, dt)}
-    print(json.dumps(line))
+    result["line"] = line
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+class _StdoutToStderr:
+    """Libraries (NCCL's version banner, warnings) may write to fd 1; the contract is ONE JSON line on stdout.
+    Everything is routed to stderr while the bench runs and the real stdout is restored for the final print."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self._saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self._saved, 1)
+        os.close(self._saved)
+        return False
+
+
 def main():
     args = parse()
-    if args.impl == "reference":
-        return run_reference(args)
-    return run_ours(args)
+    result = {}
+    with _StdoutToStderr():
+        rc = run_reference(args, result) if args.impl == "reference" else run_ours(args, result)
+    if "line" in result:
+        print(json.dumps(result["line"]))
+        sys.stdout.flush()
+    return rc
 
 
 if __name__ == "__main__":
