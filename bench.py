@@ -268,6 +268,28 @@ def run_ours(args, result):
     g1.record()
     torch.cuda.synchronize()
     gram_ms = g0.elapsed_time(g1) / reps
+    # ---- the dominant kernel alone: pass 2 (k_tri_gram + its finish) through nb_matmul_f64, which routes the
+    # symmetric X^T diag(w) X to the same kernel nb_glm_stats uses
+    wbuf = dv.empty((n,), np.float64, local)
+    _lib.check(lib.nb_fill(local, n, wbuf.ptr, wbuf.code, 0.25, 0, st))
+    Gm = dv.empty((d, d), np.float64, local)
+    sc2 = dv.scratch(lib.nb_matmul_scratch_bytes(local, d, d, n), local)
+
+    def tri():
+        _lib.check(lib.nb_matmul_f64(local, d, d, n, X.ptr, 1, d, X.ptr, d, 1, wbuf.ptr, Gm.ptr, d,
+                                     sc2.data_ptr(), sc2.numel(), st))
+
+    for _ in range(3):
+        tri()
+    torch.cuda.synchronize()
+    t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0e.record()
+    for _ in range(reps):
+        tri()
+    t1e.record()
+    torch.cuda.synchronize()
+    tri_ms = t0e.elapsed_time(t1e) / reps
+    del wbuf, Gm, sc2
     # pass 1 alone (HBM-bound link / gradient pass = the L-BFGS evaluation)
     for _ in range(2):
         fused.glm_stats(X, y, beta_d, "logistic", False)
@@ -344,6 +366,14 @@ def run_ours(args, result):
         fp64_peak = json.load(open(os.path.join(ROOT, "profiles", "fp64_peak.json"))).get("dmma_tflops")
     except Exception:
         pass
+    traffic = None       # dram__bytes_read.sum + dram__bytes_write.sum of one k_tri_gram launch (ncu --set full)
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if int(tr.get("rows", -1)) == n and int(tr.get("d", -1)) == d:
+            traffic = tr.get("k_tri_gram_dram_bytes")
+    except Exception:
+        pass
+    executed_flops = 2.0 * n * 1024 * (((d + 31) // 32) * ((d + 31) // 32 + 1) // 2)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -354,20 +384,21 @@ def run_ours(args, result):
                    "step": "one Newton iteration: fused stats pass + all-reduce(p*p+p+1 f64) + Newton update + 8-byte read-back"},
         "fit_sec_per_iteration": ms_step * 1e-3,
         "fit_sec": fit_sec, "fit_iterations": fit_iters,
-        "roofline": {"bound": "hbm", "kernel": "nb_glm_stats(want_hess=1): k_glm_rows (pass 1, HBM-bound) + k_tri_gram (pass 2: warp-specialised "
-                               "upper-triangular X^T diag(w) X, FP64 DMMA fed by TMA bulk copies) + finish kernels",
-                     "achieved": gram_bytes / (gram_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": gram_bytes / (gram_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
-                     "ms_per_launch": gram_ms,
+        "roofline": {"bound": "hbm",
+                     "kernel": "k_tri_gram (pass 2: warp-specialised upper-triangular X^T diag(w) X, FP64 DMMA fed by TMA "
+                               "bulk copies) + k_fused_finish, timed alone with CUDA events on its stream",
+                     "achieved": gram_bytes / (tri_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": gram_bytes / (tri_ms * 1e-3) / 1e9 / hbm_peak, "traffic": traffic, "peak_source": peak_src,
+                     "ms_per_launch": tri_ms, "algorithmic_bytes_per_launch": gram_bytes,
                      "note": "FP64-tensor-bound at d=256 (32 flop/B vs a balance of ~5.7): the DMMA ceiling is "
                              "n*d*(d+1)/37.2e12 s = 18% of the HBM peak; see fp64 (tensor roofline) and pass1 (HBM-bound pass)"},
-        "fp64": {"kernel": "k_tri_gram (pass 2 alone = stats pass - pass 1)", "ms_per_launch": gram_ms - rows_ms,
-                 "achieved_tflops_sym": gram_flops_sym / ((gram_ms - rows_ms) * 1e-3) / 1e12,
-                 "achieved_tflops_executed": 2.0 * n * 1024 * (((d + 31) // 32) * ((d + 31) // 32 + 1) // 2)
-                 / ((gram_ms - rows_ms) * 1e-3) / 1e12,
+        "fp64": {"kernel": "k_tri_gram", "ms_per_launch": tri_ms,
+                 "achieved_tflops_sym": gram_flops_sym / (tri_ms * 1e-3) / 1e12,
+                 "achieved_tflops_executed": executed_flops / (tri_ms * 1e-3) / 1e12,
                  "peak_tflops": fp64_peak,
-                 "frac_executed": (2.0 * n * 1024 * (((d + 31) // 32) * ((d + 31) // 32 + 1) // 2)
-                                   / ((gram_ms - rows_ms) * 1e-3) / 1e12 / fp64_peak) if fp64_peak else None},
+                 "frac_executed": (executed_flops / (tri_ms * 1e-3) / 1e12 / fp64_peak) if fp64_peak else None},
+        "stats_pass": {"what": "nb_glm_stats(want_hess=1) = pass 1 + pass 2 + finish kernels", "ms_per_launch": gram_ms,
+                       "achieved": gram_bytes / (gram_ms * 1e-3) / 1e9, "unit": "GB/s"},
         "pass1": {"kernel": "k_glm_rows (eta/link/objective/gradient, HBM-bound)", "ms_per_launch": rows_ms,
                   "achieved": gram_bytes / (rows_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                   "frac": gram_bytes / (rows_ms * 1e-3) / 1e9 / hbm_peak},
