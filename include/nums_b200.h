@@ -143,6 +143,27 @@ int nb_copy_strided(int device, int ndim, const int64_t* shape, int itemsize,
 int nb_pcg64_random(int device, int64_t n, const uint64_t* state_hi_lo, const uint64_t* inc_hi_lo,
                     double* out_d, void* stream);
 
+/* rfunc "normal" / "standard_normal" (random.py:158-195 -> numpy_kernel.py:103-110): n doubles in the order
+ * Generator(PCG64(seed).jumped(j)).normal(loc, scale, n) returns them.  NumPy's ziggurat consumes a
+ * data-dependent number of words per value; the device resolves that with a prefix scan of per-chunk state
+ * maps (csrc/rng_scan.cu), so element i is the host generator's i-th value: identical bits wherever the
+ * value is a table product (99.97 % of draws), within 1 ulp of libm's log1p on the tail draws.
+ * standard != 0 returns the values unscaled (standard_normal).  The call reads back one 8-byte count and
+ * therefore synchronises `stream`; it fails if the scanned words yielded fewer than n values. */
+int64_t nb_pcg64_normal_scratch_bytes(int64_t n);
+int nb_pcg64_normal(int device, int64_t n, const uint64_t* state_hi_lo, const uint64_t* inc_hi_lo,
+                    double loc, double scale, int standard, double* out_d,
+                    void* scratch_d, int64_t scratch_bytes, void* stream);
+
+/* rfunc "integers" with dtype int64 (random.py:158-195): out[i] = low + (i-th bounded draw over [0, rng]),
+ * rng = high - low - 1 (or high - low with endpoint=True), bit-identical to Generator.integers: Lemire's
+ * multiply-shift on 32-bit half-words when rng < 2^32 (low half first), on 64-bit words otherwise, with its
+ * rejections placed by the same prefix scan.  Synchronises `stream` when the range needs rejection. */
+int64_t nb_pcg64_integers_scratch_bytes(int64_t n, uint64_t rng);
+int nb_pcg64_integers(int device, int64_t n, const uint64_t* state_hi_lo, const uint64_t* inc_hi_lo,
+                      int64_t low, uint64_t rng, int64_t* out_d,
+                      void* scratch_d, int64_t scratch_bytes, void* stream);
+
 /* ---- reductions: KernelCls.reduce_axis :294-313, sum_reduce :291, bop_reduce :433-453 -- */
 
 /* Views the input as [outer, len, inner] (C order) and reduces the middle axis:

@@ -5,36 +5,13 @@
 // 128-bit (state, inc) and every thread jumps to its own position with the O(log k) LCG advance, then
 // strides through the sequence with the grid-wide jump (a^T, c_T): element i is produced by exactly the
 // i-th step of the stream, whatever the launch geometry.
-#include "common.cuh"
+#include "pcg64.cuh"
 
 namespace nb {
 
-typedef unsigned __int128 u128;
-
-__device__ __forceinline__ u128 make128(uint64_t hi, uint64_t lo) { return ((u128)hi << 64) | (u128)lo; }
-
-// (mult, plus) such that state_{k} = mult * state_0 + plus  (pcg_advance_lcg_128)
-__device__ __forceinline__ void lcg_advance(u128 a, u128 c, uint64_t delta, u128& mult, u128& plus) {
-  u128 acc_m = 1, acc_p = 0, cur_m = a, cur_p = c;
-  while (delta > 0) {
-    if (delta & 1) { acc_m *= cur_m; acc_p = acc_p * cur_m + cur_p; }
-    cur_p = (cur_m + 1) * cur_p;
-    cur_m *= cur_m;
-    delta >>= 1;
-  }
-  mult = acc_m; plus = acc_p;
-}
-
-__device__ __forceinline__ uint64_t xsl_rr(u128 s) {
-  const uint64_t hi = (uint64_t)(s >> 64), lo = (uint64_t)s;
-  const uint64_t x = hi ^ lo;
-  const unsigned rot = (unsigned)(hi >> 58);
-  return (x >> rot) | (x << ((64u - rot) & 63u));
-}
-
 __global__ void __launch_bounds__(256)
 k_pcg64_random(int64_t n, uint64_t s_hi, uint64_t s_lo, uint64_t i_hi, uint64_t i_lo, double* __restrict__ out) {
-  const u128 a = make128(0x2360ED051FC65DA4ull, 0x4385DF649FCCF645ull);   // PCG_DEFAULT_MULTIPLIER_128
+  const u128 a = NB_PCG_MULT;
   const u128 inc = make128(i_hi, i_lo);
   const uint64_t T = (uint64_t)gridDim.x * 256;
   const uint64_t t = (uint64_t)blockIdx.x * 256 + threadIdx.x;

@@ -100,27 +100,79 @@ class KernelCls:
         return out
 
     def random_block(self, rng_params, rfunc_name, rfunc_args, shape, dtype, device_index=None):
-        # numpy_kernel.py:103-110.  Uniform doubles are generated on the device, bit-identical to the host
-        # stream; every other distribution is drawn by the reference's own host RNG and uploaded (ziggurat /
-        # rejection samplers consume a data-dependent number of draws); see DESIGN.md "inputs".
-        if rfunc_name == "random" and len(rfunc_args) == 1 and np.dtype(dtype) == np.dtype(np.float64):
-            return self._random_on_device(rng_params, int(rfunc_args[0]), shape, _cur(device_index))
+        # numpy_kernel.py:103-110.  random / normal / standard_normal (float64) and integers (int64) are generated in
+        # HBM in the host generator's order (csrc/rng.cu, csrc/rng_scan.cu); the remaining distributions are drawn
+        # by the reference's own host RNG and uploaded; see DESIGN.md "inputs".
+        dev = _cur(device_index)
+        f64 = np.dtype(dtype) == np.dtype(np.float64)
+        if rfunc_name == "random" and len(rfunc_args) == 1 and f64:
+            return self._random_on_device(rng_params, int(rfunc_args[0]), shape, dev)
+        if rfunc_name == "normal" and len(rfunc_args) == 3 and f64 and np.isscalar(rfunc_args[0]) \
+                and np.isscalar(rfunc_args[1]):
+            loc, scale, size = rfunc_args
+            if scale < 0:
+                raise ValueError("scale < 0")
+            return self._normal_on_device(rng_params, int(size), shape, dev, float(loc), float(scale), False)
+        if rfunc_name == "standard_normal" and len(rfunc_args) == 1 and f64:
+            return self._normal_on_device(rng_params, int(rfunc_args[0]), shape, dev, 0.0, 1.0, True)
+        if rfunc_name == "integers" and len(rfunc_args) == 5:
+            low, high, size, idt, endpoint = rfunc_args
+            if np.dtype(idt) == np.dtype(np.int64) and np.isscalar(low) and (high is None or np.isscalar(high)):
+                return self._integers_on_device(rng_params, low, high, int(size), bool(endpoint), shape, dev)
         rng = block_rng(*rng_params)
         result = getattr(rng, rfunc_name)(*rfunc_args).reshape(shape)
         if rfunc_name not in ("random", "integers"):
             result = result.astype(dtype)
-        return dv.from_numpy(result, _cur(device_index))
+        return dv.from_numpy(result, dev)
 
-    def _random_on_device(self, rng_params, size, shape, dev):
-        """Uniform doubles generated in HBM, bit-identical to the host stream: NumPy seeds and jumps the
-        bit generator, the device produces the values (nb_pcg64_random)."""
+    @staticmethod
+    def _stream_state(rng_params):
+        """NumPy seeds and jumps the bit generator (SeedSequence + PCG64.jumped stay on the host); the device gets
+        the block's 128-bit LCG state and increment as {hi, lo} pairs."""
         seed, jump = rng_params
         st = PCG64(seed).jumped(jump).state["state"]
         mask = (1 << 64) - 1
-        state = (C.c_uint64 * 2)(st["state"] >> 64, st["state"] & mask)
-        inc = (C.c_uint64 * 2)(st["inc"] >> 64, st["inc"] & mask)
+        return ((C.c_uint64 * 2)(st["state"] >> 64, st["state"] & mask),
+                (C.c_uint64 * 2)(st["inc"] >> 64, st["inc"] & mask))
+
+    def _random_on_device(self, rng_params, size, shape, dev):
+        """Uniform doubles generated in HBM, bit-identical to the host stream (nb_pcg64_random)."""
+        state, inc = self._stream_state(rng_params)
         out = dv.empty((size,), np.float64, dev)
         _lib.check(_lib.load().nb_pcg64_random(dev, size, state, inc, out.ptr, dv.stream_ptr(dev)))
+        return DeviceBlock(out.t.view(tuple(shape)))
+
+    def _normal_on_device(self, rng_params, size, shape, dev, loc, scale, standard):
+        """Generator.normal / standard_normal in HBM, in the host generator's order (nb_pcg64_normal)."""
+        lib = _lib.load()
+        state, inc = self._stream_state(rng_params)
+        out = dv.empty((size,), np.float64, dev)
+        sc = dv.scratch(lib.nb_pcg64_normal_scratch_bytes(size), dev)
+        _lib.check(lib.nb_pcg64_normal(dev, size, state, inc, loc, scale, 1 if standard else 0, out.ptr,
+                                       sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+        return DeviceBlock(out.t.view(tuple(shape)))
+
+    def _integers_on_device(self, rng_params, low, high, size, endpoint, shape, dev):
+        """Generator.integers(low, high, size, int64, endpoint) in HBM, bit-identical (nb_pcg64_integers)."""
+        if high is None:
+            low, high = 0, low
+        low, high = int(low), int(high)
+        if not endpoint:
+            high -= 1
+        lo64, hi64 = -(1 << 63), (1 << 63) - 1
+        if low < lo64:
+            raise ValueError("low is out of bounds for int64")
+        if high > hi64:
+            raise ValueError("high is out of bounds for int64")
+        if low > high:
+            raise ValueError("low > high" if endpoint else "low >= high")
+        lib = _lib.load()
+        state, inc = self._stream_state(rng_params)
+        out = dv.empty((size,), np.int64, dev)
+        rng = high - low
+        sc = dv.scratch(lib.nb_pcg64_integers_scratch_bytes(size, rng), dev)
+        _lib.check(lib.nb_pcg64_integers(dev, size, state, inc, low, rng, out.ptr, sc.data_ptr(), sc.numel(),
+                                         dv.stream_ptr(dev)))
         return DeviceBlock(out.t.view(tuple(shape)))
 
     def permutation(self, rng_params, size, device_index=None):

@@ -318,8 +318,55 @@ def test_device_block_rng_uniform_is_bit_identical(K, n, jump):
     mat = down(K.random_block((42, jump), "random", (6 * 7,), (6, 7), np.float64, device_index=0))
     np.testing.assert_array_equal(mat, ok.random_block((42, jump), "random", (6 * 7,), (6, 7), np.float64))
     # other distributions still come from the host stream, unchanged
-    z = down(K.random_block((1337, jump), "normal", (0.0, 1.0, 257), (257,), np.float64, device_index=0))
-    np.testing.assert_array_equal(z, ok.random_block((1337, jump), "normal", (0.0, 1.0, 257), (257,), np.float64))
+    # a distribution that stays on the host generator (uploaded): same stream by construction
+    z = down(K.random_block((1337, jump), "exponential", (2.0, 257), (257,), np.float64, device_index=0))
+    np.testing.assert_array_equal(z, ok.random_block((1337, jump), "exponential", (2.0, 257), (257,), np.float64))
+
+
+@pytest.mark.parametrize("n,jump", [(1, 0), (63, 1), (64, 2), (65, 3), (1000, 4), (100_003, 5), (5_000_000, 17)])
+def test_device_block_rng_normal_follows_the_host_ziggurat(K, n, jump):
+    """random_block("normal") is generated in HBM (csrc/rng_scan.cu) in the order of the reference's
+    Generator(PCG64(seed).jumped(jump)).normal(loc, scale, n) (numpy_kernel.py:31-32,103-110; random.py:158-195).
+    Values that are table products are bit-identical; the 0.03 % drawn from the tail go through log1p, where the
+    device's libm may differ from the host's in the last place.  One misplaced rejection would shift every later
+    element, so element-wise agreement over millions of draws pins the word-consumption logic."""
+    for args, name in (((0.0, 1.0, n), "normal"), ((-3.5, 2.25, n), "normal"), ((n,), "standard_normal")):
+        got = down(K.random_block((1337, jump), name, args, (n,), np.float64, device_index=0))
+        want = ok.random_block((1337, jump), name, args, (n,), np.float64)
+        assert got.shape == want.shape and got.dtype == want.dtype
+        differs = got != want
+        assert differs.mean() <= 2e-3, (name, args[:2], differs.mean())
+        np.testing.assert_allclose(got, want, rtol=4e-16, atol=0)
+        body = np.abs(want if name == "standard_normal" else (want - args[0]) / args[1]) < 3.6
+        np.testing.assert_array_equal(got[body], want[body])
+    mat = down(K.random_block((7, jump), "normal", (1.0, 0.5, 12 * 5), (12, 5), np.float64, device_index=0))
+    np.testing.assert_array_equal(mat, ok.random_block((7, jump), "normal", (1.0, 0.5, 12 * 5), (12, 5), np.float64))
+
+
+INT_RANGES = [
+    (0, 10, False), (-5, 5, True), (3, 3, True), (0, 2 ** 31 + 12345, False), (0, 2 ** 32, False),
+    (-7, 2 ** 32 + 5, False), (-2 ** 62, 2 ** 62, False), (0, 3 * 2 ** 61, False), (-2 ** 63, 2 ** 63 - 1, True),
+    (10 ** 8, None, False), (0, 2 ** 20, False),
+]
+
+
+@pytest.mark.parametrize("low,high,endpoint", INT_RANGES)
+def test_device_block_rng_integers_is_bit_identical(K, low, high, endpoint):
+    """random_block("integers", dtype=int64): Lemire rejection on 32-bit half-words / 64-bit words, constant, raw 32
+    and raw 64-bit ranges, all in the host generator's order (random.py:173-178 argument order)."""
+    for n, jump in ((1, 0), (129, 1), (1_000_003, 2)):
+        args = (low, high, n, np.int64, endpoint)
+        got = down(K.random_block((99, jump), "integers", args, (n,), np.int64, device_index=0))
+        want = ok.random_block((99, jump), "integers", args, (n,), np.int64)
+        assert got.dtype == want.dtype == np.int64
+        np.testing.assert_array_equal(got, want)
+
+
+def test_device_block_rng_integers_rejects_bad_bounds(K):
+    with pytest.raises(ValueError):
+        K.random_block((1, 0), "integers", (5, 5, 10, np.int64, False), (10,), np.int64, device_index=0)
+    with pytest.raises(ValueError):
+        K.random_block((1, 0), "integers", (0, 2 ** 63 + 1, 10, np.int64, False), (10,), np.int64, device_index=0)
 
 
 @pytest.mark.parametrize("m,n,k", [(1664, 1664, 512), (1666, 1730, 1002), (2048, 1540, 70)])

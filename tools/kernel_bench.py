@@ -145,6 +145,22 @@ def main():
     S = dv.from_numpy(S.T @ S + np.eye(257), 0)
     add("inv 257 x 257", "numpy_kernel.py:471", timeit(lambda: K.inv(S), reps=5))
 
+    # block RNG in HBM: same values as the host generator, which is timed on 10^7 draws beside it
+    import time as _t
+    from numpy.random import PCG64, Generator
+    for name, rargs, dt_ in (("random", (n,), np.float64), ("normal", (0.0, 1.0, n), np.float64),
+                             ("integers", (0, 10 ** 6, n, np.int64, False), np.int64),
+                             ("integers", (0, 3 * 2 ** 61, n, np.int64, False), np.int64)):
+        hn = 10 ** 7
+        hargs = tuple(hn if a == n else a for a in rargs)
+        g = Generator(PCG64(1337).jumped(3))
+        t0 = _t.perf_counter()
+        getattr(g, name)(*hargs)
+        host_ms = (_t.perf_counter() - t0) * 1e3 * (n / hn)
+        label = "random_block %s%s n=%d (host NumPy: %.0f ms, extrapolated from 10^7)" % (
+            name, "" if name != "integers" else " [0,%.3g)" % rargs[1], n, host_ms)
+        add(label, "numpy_kernel.py:103-110", timeit(lambda: K.random_block((1337, 3), name, rargs, (n,), dt_, device_index=0), reps=3), 8 * n)
+
     # BASELINE config 1: the README fit (10^6 x 2, newton-cg, l2, C=10), wall clock incl. host control flow
     import time
     import warnings
