@@ -231,6 +231,28 @@ size_t nb_inv_scratch_bytes(int64_t p);
 int nb_inv_f64(int device, int64_t p, const double* a_d, double* out_d, int32_t* info_d,
                void* scratch_d, size_t scratch_bytes, void* stream);
 
+/* ---- KernelCls.cholesky / qr / svd (numpy_kernel.py:455-469): the p x p ends of the tall-skinny routines of
+ *      nums/core/linalg.py:55-243 (indirect_tsr, direct_tsqr, svd, pca); p <= 1024 --------------------------- */
+
+/* l = lower Cholesky factor of the symmetric positive definite a (np.linalg.cholesky, numpy_kernel.py:463-464;
+ * only the lower triangle of a is read).  *info_d = 0, or j+1 when the leading minor of order j+1 is not positive. */
+int nb_cholesky_f64(int device, int64_t p, const double* a_d, double* l_d, int32_t* info_d, void* stream);
+
+/* Signs of diag(R) that np.linalg.qr (LAPACK dgeqrf, numpy_kernel.py:455-461) gives for a matrix whose
+ * positive-diagonal QR factor has the top p x p block qtop (row-major, leading dimension ldq): signs_d[j] = +-1,
+ * R = diag(signs) R+, Q = Q+ diag(signs).  `square` != 0 when the factored matrix is p x p (LAPACK's last
+ * reflector is then the identity). */
+int64_t nb_qr_signs_scratch_bytes(int64_t p);
+int nb_qr_signs_f64(int device, int64_t p, const double* qtop_d, int64_t ldq, int square, double* signs_d,
+                    void* scratch_d, int64_t scratch_bytes, void* stream);
+
+/* a = u diag(s) vt for a square p x p matrix (np.linalg.svd, numpy_kernel.py:466-469), singular values in
+ * descending order, by one-sided Jacobi.  The signs of paired columns of u / rows of vt are not LAPACK's (any
+ * consistent choice is a valid SVD).  *info_d = sweeps used, or -1 if 60 sweeps did not converge. */
+int64_t nb_svd_scratch_bytes(int64_t p);
+int nb_svd_f64(int device, int64_t p, const double* a_d, double* u_d, double* s_d, double* vt_d,
+               int32_t* info_d, void* scratch_d, int64_t scratch_bytes, void* stream);
+
 /* ---- the GLM inner loop: glms.py:457-499 (Logistic), :275-327 (Linear), :515-556 (Poisson)
  *      as called from newton() :660-676 and LBFGS lbfgs.py:102-155 ------------------------ */
 

@@ -53,6 +53,11 @@ SIGNATURES = {
     "nb_matmul_i64": (c_int, [c_int, c_i64, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_vp]),
     "nb_inv_scratch_bytes": (c_sz, [c_i64]),
     "nb_inv_f64": (c_int, [c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "nb_cholesky_f64": (c_int, [c_int, c_i64, c_vp, c_vp, c_vp, c_vp]),
+    "nb_qr_signs_scratch_bytes": (c_i64, [c_i64]),
+    "nb_qr_signs_f64": (c_int, [c_int, c_i64, c_vp, c_i64, c_int, c_vp, c_vp, c_i64, c_vp]),
+    "nb_svd_scratch_bytes": (c_i64, [c_i64]),
+    "nb_svd_f64": (c_int, [c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "nb_glm_stats_len": (c_i64, [c_i64]),
     "nb_glm_scratch_bytes": (c_sz, [c_int, c_i64, c_i64, c_int]),
     "nb_glm_stats": (c_int, [c_int, c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_sz, c_vp]),

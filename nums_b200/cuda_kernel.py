@@ -556,14 +556,136 @@ class KernelCls:
             raise np.linalg.LinAlgError("Singular matrix")
         return out
 
+    # ---------------------------------------------------------------- factorisations
+    def _f64_matrix(self, arr, dev):
+        src = dv.contiguous(dv.to_device(arr, dev))
+        if src.ndim != 2:
+            raise np.linalg.LinAlgError("%d-dimensional array given. Array must be two-dimensional" % src.ndim)
+        if src.dtype != np.dtype(np.float64):
+            src = self.astype(src, "float64")
+        return src
+
+    def _chol_lower(self, a, dev):
+        """Lower Cholesky factor or None when a is not positive definite (one 4-byte read-back)."""
+        lib = _lib.load()
+        p = a.shape[0]
+        out = dv.empty((p, p), np.float64, dev)
+        info = dv.empty((1,), np.int32, dev)
+        _lib.check(lib.nb_cholesky_f64(dev, p, a.ptr, out.ptr, info.ptr, dv.stream_ptr(dev)))
+        return out if int(dv.to_numpy(info)[0]) == 0 else None
+
+    def _cholqr_pass(self, Y, dev, shift=0.0):
+        """One Cholesky-QR pass: Y = Q R with R = chol(Y^T Y + shift I)^T.  Returns (Q, R) or None."""
+        n = Y.shape[1]
+        G = self.bop("tensordot", Y, Y, True, False, 1)
+        if shift:
+            eye = dv.empty((n, n), np.float64, dev)
+            _lib.check(_lib.load().nb_eye(dev, n, n, eye.ptr, eye.code, dv.stream_ptr(dev)))
+            G = self.bop("add", G, self.bop("mul", eye, dv.from_numpy(np.float64(shift), dev), False, False, {}),
+                         False, False, {})
+        L = self._chol_lower(G, dev)
+        if L is None:
+            return None
+        R = dv.contiguous(L.T)
+        Rinv = self.inv(R)
+        return self.bop("tensordot", Y, Rinv, False, False, 1), R, Rinv
+
     def qr(self, *arrays, mode="reduced", axis=None):
-        _unsupported("qr")
+        """numpy_kernel.py:455-461: np.linalg.qr of the concatenated operands, modes "r" and "reduced".
+
+        Tall-skinny (m >= n) on the device as CholeskyQR2: R1 = chol(X^T X)^T, Q1 = X R1^-1, R2 = chol(Q1^T Q1)^T,
+        R = R2 R1, Q = Q1 R2^-1 -- two passes over X on the FP64 tensor-core Gram/GEMM kernels, orthogonality at
+        rounding level for cond(X) < ~1e8; when the first Cholesky breaks down the shifted three-pass variant
+        (Fukaya et al. 2020) is used.  LAPACK's sign convention for diag(R) is then restored from the top n x n
+        block of Q (nb_qr_signs_f64), so the factors agree with the reference's to rounding, not just up to signs."""
+        dev = _dev(*arrays)
+        if mode not in ("r", "reduced"):
+            raise NotImplementedError("qr mode '%s'" % mode)
+        in_dtype = arrays[0].dtype
+        if len(arrays) > 1:
+            assert axis is not None
+            mats = [self._f64_matrix(a, dev) for a in arrays]
+            import torch
+            X = DeviceBlock(torch.cat([b.t for b in mats], dim=axis))
+        else:
+            X = self._f64_matrix(arrays[0], dev)
+        m, n = X.shape
+        if m < n:
+            raise NotImplementedError("qr of a wide block (%d x %d): the device path is tall-skinny only" % (m, n))
+        lib = _lib.load()
+        st = dv.stream_ptr(dev)
+        first = self._cholqr_pass(X, dev)
+        passes = []
+        if first is None:
+            # shifted CholeskyQR3: the shift makes the first Gram matrix safely positive definite
+            fro2 = float(dv.to_numpy(self.bop("tensordot", DeviceBlock(X.t.reshape(-1)),
+                                             DeviceBlock(X.t.reshape(-1)), False, False, 1)))
+            shift = 11.0 * (m * n + n * (n + 1)) * np.finfo(np.float64).eps * fro2
+            first = self._cholqr_pass(X, dev, shift)
+            if first is None:
+                raise np.linalg.LinAlgError("qr: block is numerically rank deficient beyond the shifted Cholesky QR")
+            second = self._cholqr_pass(first[0], dev)
+            if second is None:
+                raise np.linalg.LinAlgError("qr: block is numerically rank deficient beyond the shifted Cholesky QR")
+            passes = [first, second]
+            Y = second[0]
+        else:
+            passes = [first]
+            Y = first[0]
+        # last pass: keep R^-1 apart so that mode "r" never forms the final Q
+        G = self.bop("tensordot", Y, Y, True, False, 1)
+        L = self._chol_lower(G, dev)
+        if L is None:
+            raise np.linalg.LinAlgError("qr: Gram matrix of the orthogonalised block is not positive definite")
+        R = dv.contiguous(L.T)
+        Rinv = self.inv(R)
+        for _, Rp, _ in reversed(passes):
+            R = self.bop("tensordot", R, Rp, False, False, 1)
+        # Householder signs from the top n x n block of Q+
+        Ytop = dv.contiguous(DeviceBlock(Y.t[:n]))
+        Qtop = self.bop("tensordot", Ytop, Rinv, False, False, 1)
+        signs = dv.empty((n,), np.float64, dev)
+        sc = dv.scratch(lib.nb_qr_signs_scratch_bytes(n), dev)
+        _lib.check(lib.nb_qr_signs_f64(dev, n, Qtop.ptr, n, 1 if m == n else 0, signs.ptr, sc.data_ptr(), sc.numel(), st))
+        R = self.bop("mul", DeviceBlock(signs.t.view(n, 1)), R, False, False, {})
+        back = (lambda b: b) if in_dtype == np.dtype(np.float64) else (lambda b: self.astype(b, in_dtype.name))
+        if mode == "r":
+            return back(R)
+        Rinv_s = self.bop("mul", Rinv, DeviceBlock(signs.t.view(1, n)), False, False, {})
+        Q = self.bop("tensordot", Y, Rinv_s, False, False, 1)
+        return back(Q), back(R)
 
     def cholesky(self, arr):
-        _unsupported("cholesky")
+        # numpy_kernel.py:463-464
+        dev = arr.device_index
+        a = self._f64_matrix(arr, dev)
+        if a.shape[0] != a.shape[1]:
+            raise np.linalg.LinAlgError("Last 2 dimensions of the array must be square")
+        L = self._chol_lower(a, dev)
+        if L is None:
+            raise np.linalg.LinAlgError("Matrix is not positive definite")
+        return L if arr.dtype == np.dtype(np.float64) else self.astype(L, arr.dtype.name)
 
     def svd(self, arr):
-        _unsupported("svd")
+        # numpy_kernel.py:466-469 for the square R of a tall-skinny factorisation (linalg.py:221-223)
+        dev = arr.device_index
+        a = self._f64_matrix(arr, dev)
+        p = a.shape[0]
+        if a.shape[1] != p:
+            raise NotImplementedError("svd of a non-square block (%d x %d)" % a.shape)
+        lib = _lib.load()
+        U = dv.empty((p, p), np.float64, dev)
+        S = dv.empty((p,), np.float64, dev)
+        VT = dv.empty((p, p), np.float64, dev)
+        info = dv.empty((1,), np.int32, dev)
+        sc = dv.scratch(lib.nb_svd_scratch_bytes(p), dev)
+        _lib.check(lib.nb_svd_f64(dev, p, a.ptr, U.ptr, S.ptr, VT.ptr, info.ptr, sc.data_ptr(), sc.numel(),
+                                  dv.stream_ptr(dev)))
+        if int(dv.to_numpy(info)[0]) < 0:
+            raise np.linalg.LinAlgError("SVD did not converge")
+        if arr.dtype != np.dtype(np.float64):
+            U, S, VT = (self.astype(b, arr.dtype.name) for b in (U, S, VT))
+        return U, S, VT
 
     def einsum(self, subscript, *operands):
         _unsupported("einsum")
