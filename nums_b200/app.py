@@ -165,6 +165,22 @@ class ArrayApplication:
         count = int(np.prod(X.shape)) if axis is None else X.shape[axis]
         return self.sum(X, axis=axis, keepdims=keepdims) / count
 
+    def cov(self, X, rowvar=True, bias=False, dtype=None):
+        # application.py:531-540
+        n = X.shape[1] if rowvar else X.shape[0]
+        const = n if bias else n - 1
+        Xc = X - self.mean(X, axis=(1 if rowvar else 0), keepdims=True)
+        r = (Xc @ Xc.transpose(defer=True) if rowvar else Xc.transpose(defer=True) @ Xc) / const
+        return r if dtype is None else r.astype(dtype)
+
+    def vec_from_oids(self, oids, shape, block_shape, dtype):
+        # application.py:1168-1180: blocks handed over as a vector of object ids, then re-blocked
+        shape, block_shape = tuple(shape), tuple(block_shape)
+        arr = BlockArray(ArrayGrid(shape=shape, block_shape=shape, dtype=np.dtype(dtype).name), self.km)
+        for i, entry in enumerate(arr.grid.get_entry_iterator()):
+            arr.blocks[entry].oid = oids[i]
+        return arr if block_shape == shape else arr.reshape(block_shape=block_shape)
+
     def norm(self, X, order=2):
         assert X.ndim == 1 and order in (1, 2)
         if order == 2:

@@ -144,21 +144,65 @@ class BlockArray:
     def T(self):
         return self.transpose(defer=False)
 
-    def reshape(self, shape, block_shape):
-        """Vector <-> column reshapes that keep the block boundaries (what glms.py:495 needs)."""
-        shape, block_shape = tuple(shape), tuple(block_shape)
+    def copy(self):
+        """base.py:337-345: a new BlockArray over the same (immutable) block objects."""
+        out = BlockArray(self.grid.copy(), self.km)
+        for entry in self.grid.get_entry_iterator():
+            sb, ob = self.blocks[entry], out.blocks[entry]
+            ob.oid, ob.transposed = sb.oid, sb.transposed
+        return out
+
+    def reshape(self, shape=None, block_shape=None):
+        """blockarray.py:1135-1290 (Reshape) for the cases the path needs: vector <-> column reshapes that keep the
+        block boundaries (glms.py:495) and re-blocking at constant shape (linalg.py:96-103, vec_from_oids)."""
+        shape = self.shape if shape is None else tuple(shape)
+        block_shape = self.block_shape if block_shape is None else tuple(block_shape)
+        if shape == self.shape and block_shape == self.block_shape:
+            return self
+        if shape == self.shape:
+            return self._reblock(block_shape)
         grid = ArrayGrid(shape, block_shape, self.grid.dtype)
         if int(np.prod(grid.grid_shape)) != int(np.prod(self.grid.grid_shape)):
-            raise NotImplementedError("reshape that changes the block partition")
+            raise NotImplementedError("reshape that changes both the shape and the block partition")
         out = BlockArray(grid, self.km)
         for src, dst in zip(self.grid.get_entry_iterator(), grid.get_entry_iterator()):
             sb, db = self.blocks[src], out.blocks[dst]
             if int(np.prod(sb.shape)) != int(np.prod(db.shape)):
-                raise NotImplementedError("reshape that changes the block partition")
+                raise NotImplementedError("reshape that changes both the shape and the block partition")
             oid = sb.oid
             if sb.transposed:
                 oid = self.km.transpose(oid, syskwargs=sb.syskwargs())
             db.oid = self.km.reshape(oid, db.shape, syskwargs=db.syskwargs())
+        return out
+
+    def _reblock(self, block_shape):
+        """Same array, new block partition: every destination block gathers the rectangles of the source blocks it
+        overlaps with one create_block call (blockarray.py:1245-1251 -> numpy_kernel.py:116-129)."""
+        grid = ArrayGrid(self.shape, block_shape, self.grid.dtype)
+        out = BlockArray(grid, self.km)
+        nd = len(self.shape)
+
+        def overlaps(ax, lo, hi):
+            bs = self.block_shape[ax]
+            first, last = lo // bs, (hi - 1) // bs
+            for g in range(first, last + 1):
+                s_lo, s_hi = g * bs, min((g + 1) * bs, self.shape[ax])
+                a, b = max(lo, s_lo), min(hi, s_hi)
+                yield g, slice(a - s_lo, b - s_lo), slice(a - lo, b - lo)
+
+        for entry in grid.get_entry_iterator():
+            dst_slices = grid.get_slice(entry)
+            per_axis = [list(overlaps(ax, dst_slices[ax].start, dst_slices[ax].stop)) for ax in range(nd)]
+            oids, src_params, dst_params = [], [], []
+            for combo in itertools.product(*per_axis):
+                src_entry = tuple(c[0] for c in combo)
+                sb = self.blocks[src_entry]
+                oids.append(sb.oid)
+                src_params.append((tuple(c[1] for c in combo), sb.transposed))
+                dst_params.append((tuple(c[2] for c in combo), False))
+            db = out.blocks[entry]
+            db.oid = self.km.create_block(*oids, src_params=src_params, dst_params=dst_params, dst_shape=db.shape,
+                                          dst_shape_bc=None, syskwargs=db.syskwargs())
         return out
 
     def astype(self, dtype):

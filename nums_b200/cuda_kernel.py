@@ -610,8 +610,15 @@ class KernelCls:
         else:
             X = self._f64_matrix(arrays[0], dev)
         m, n = X.shape
+        back = (lambda b: b) if in_dtype == np.dtype(np.float64) else (lambda b: self.astype(b, in_dtype.name))
         if m < n:
-            raise NotImplementedError("qr of a wide block (%d x %d): the device path is tall-skinny only" % (m, n))
+            # wide block (a column-blocked covariance in linalg.pca): LAPACK reflects the leading m x m part and
+            # carries the other columns along, R = [R1, Q^T A2]
+            import torch
+            Q, R1 = self.qr(dv.contiguous(DeviceBlock(X.t[:, :m])), mode="reduced")
+            R2 = self.bop("tensordot", Q, dv.contiguous(DeviceBlock(X.t[:, m:])), True, False, 1)
+            R = DeviceBlock(torch.cat([R1.t, R2.t], dim=1))
+            return back(R) if mode == "r" else (back(Q), back(R))
         lib = _lib.load()
         st = dv.stream_ptr(dev)
         first = self._cholqr_pass(X, dev)
@@ -648,7 +655,6 @@ class KernelCls:
         sc = dv.scratch(lib.nb_qr_signs_scratch_bytes(n), dev)
         _lib.check(lib.nb_qr_signs_f64(dev, n, Qtop.ptr, n, 1 if m == n else 0, signs.ptr, sc.data_ptr(), sc.numel(), st))
         R = self.bop("mul", DeviceBlock(signs.t.view(n, 1)), R, False, False, {})
-        back = (lambda b: b) if in_dtype == np.dtype(np.float64) else (lambda b: self.astype(b, in_dtype.name))
         if mode == "r":
             return back(R)
         Rinv_s = self.bop("mul", Rinv, DeviceBlock(signs.t.view(1, n)), False, False, {})

@@ -55,7 +55,12 @@ def bootstrap():
     return tmp
 
 
+ONLY = [a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--only=")]
+
+
 def save(name, **arrays):
+    if ONLY and name not in ONLY:
+        return
     path = os.path.join(HERE, name + ".npz")
     np.savez_compressed(path, **arrays)
     print("wrote %s (%.1f KB)" % (path, os.path.getsize(path) / 1024))
@@ -286,6 +291,46 @@ def main():
          sum_p=np.asarray(s.get()), argmax_p=np.asarray(am.get()), argmin_x=np.asarray(amin.get()),
          max_x=np.asarray(app.max(x).get()), mean_x=np.asarray(app.mean(x).get()),
          row_block=np.int64(n // 4))
+
+    # ---------------------------------------------------------------- tall-skinny linear algebra (linalg.py)
+    from nums.core import linalg
+    rs3 = app.random_state(2024)
+    nL, dL, rbL, cbL = 2345, 9, 123, 4                 # the shapes of tests/core/test_linalg.py:155-181
+    XL = rs3.normal(shape=(nL, dL), block_shape=(rbL, cbL)) + 0.25
+    XLh = XL.get()
+    thetaL = np.linspace(0.5, 1.5, dL)
+    yLh = XLh @ thetaL + 0.01 * np.cos(np.arange(nL))
+    yL = app.array(yLh, block_shape=(rbL,))
+    outL = {"X": XLh, "y": yLh, "row_block": np.int64(rbL), "col_block": np.int64(cbL)}
+    outL["tsr_R"] = linalg.indirect_tsr(app, XL).get()
+    q, r = linalg.indirect_tsqr(app, XL)
+    outL["itsqr_Q"], outL["itsqr_R"] = q.get(), r.get()
+    q, r = linalg.direct_tsqr(app, XL)
+    outL["dtsqr_Q"], outL["dtsqr_R"] = q.get(), r.get()
+    u, sv, vt = linalg.svd(app, XL)
+    outL["svd_U"], outL["svd_S"], outL["svd_VT"] = u.get(), sv.get(), vt.get()
+    outL["cov"] = app.cov(XL, rowvar=False).get()
+    outL["pca"] = linalg.pca(app, XL).get()
+    outL["lr_theta"] = linalg.linear_regression(app, XL, yL).get()
+    outL["fast_lr_theta"] = linalg.fast_linear_regression(app, XL, yL).get()
+    outL["rr_theta_0"] = linalg.ridge_regression(app, XL, yL, lamb=0.0).get()
+    outL["rr_theta_10"] = linalg.ridge_regression(app, XL, yL, lamb=10.0).get()
+    # single column block, ragged last row block (the tall-skinny layout of the GLM path)
+    XT = rs3.normal(shape=(2100, 32), block_shape=(512, 32))
+    outL["X_tall"] = XT.get()
+    q, r = linalg.direct_tsqr(app, XT)
+    outL["tall_dtsqr_Q"], outL["tall_dtsqr_R"] = q.get(), r.get()
+    outL["tall_tsr_R"] = linalg.indirect_tsr(app, XT).get()
+    # SPD matrix: cholesky / inv; upper-triangular blocked inverse (tests/core/test_linalg.py:128-152)
+    Ah = XLh.T @ XLh / nL + np.eye(dL)
+    A = app.array(Ah, block_shape=(cbL, cbL))
+    outL["spd"] = Ah
+    outL["chol_L"] = linalg.cholesky(app, A).get()
+    outL["inv_spd"] = linalg.inv(app, A).get()
+    Rup = np.triu(np.arange(1, 401, dtype=float).reshape(20, 20))
+    outL["uppertri"] = Rup
+    outL["inv_uppertri"] = linalg.inv_uppertri(app, app.array(Rup, block_shape=(3, 3))).get()
+    save("linalg", **outL)
 
     # ---------------------------------------------------------------- block-shape rule
     cases = [((10 ** 8,), "float64", (8, 1), 8), ((10 ** 8, 256), "float64", (8, 1), 8),

@@ -127,3 +127,33 @@ def test_lasso_elasticnet_d32(tag, kw):
     g, s = load_golden("glm_logistic_d32"), load_golden("glm_solvers_d32")
     beta, _ = oglm.fit("linear", g["X"], s["y_lin32"], int(g["row_block"]), solver="newton", **kw)
     assert rel_err(beta[:-1], s[tag + "_beta"]) < 1e-9
+
+
+# ---------------------------------------------------------------- tall-skinny linear algebra (nums/core/linalg.py)
+def test_linalg_oracle_matches_reference_outputs():
+    """oracle/linalg.py against the reference's own outputs (tests/golden/linalg.npz, shapes of the reference's
+    tests/core/test_linalg.py:155-181): identical LAPACK calls on identical blocks, so agreement is at rounding
+    level -- only the shape a BLAS product is issued in differs."""
+    from oracle import linalg as ol
+    g = load_golden("linalg")
+    X, y, rb, cb = g["X"], g["y"], int(g["row_block"]), int(g["col_block"])
+    tol = 1e-12
+    assert rel_err(ol.indirect_tsr(X, rb, cb), g["tsr_R"]) <= tol
+    for fn, tag in ((ol.indirect_tsqr, "itsqr"), (ol.direct_tsqr, "dtsqr")):
+        Q, R = fn(X, rb, cb)
+        assert rel_err(Q, g[tag + "_Q"]) <= tol and rel_err(R, g[tag + "_R"]) <= tol
+        assert rel_err(Q @ R, X) <= 1e-13
+    U, S, VT = ol.svd(X, rb, cb)
+    assert rel_err(U, g["svd_U"]) <= tol and rel_err(S, g["svd_S"]) <= tol and rel_err(VT, g["svd_VT"]) <= tol
+    assert rel_err(ol.cov(X, rb, cb), g["cov"]) <= tol
+    assert rel_err(ol.pca(X, rb, cb), g["pca"]) <= 1e-11
+    assert rel_err(ol.linear_regression(X, y, rb, cb), g["lr_theta"]) <= tol
+    assert rel_err(ol.fast_linear_regression(X, y, rb, cb), g["fast_lr_theta"]) <= tol
+    assert rel_err(ol.ridge_regression(X, y, 0.0, rb, cb), g["rr_theta_0"]) <= tol
+    assert rel_err(ol.ridge_regression(X, y, 10.0, rb, cb), g["rr_theta_10"]) <= tol
+    XT = g["X_tall"]
+    Q, R = ol.direct_tsqr(XT, 512, 32)
+    assert rel_err(Q, g["tall_dtsqr_Q"]) <= tol and rel_err(R, g["tall_dtsqr_R"]) <= tol
+    assert rel_err(ol.indirect_tsr(XT, 512, 32), g["tall_tsr_R"]) <= tol
+    assert rel_err(ol.inv_uppertri(g["uppertri"], 3), g["inv_uppertri"]) <= tol
+    assert rel_err(np.linalg.cholesky(g["spd"]), g["chol_L"]) <= tol
