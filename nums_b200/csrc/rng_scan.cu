@@ -5,11 +5,17 @@
 // A sequential sampler reads the 64-bit word stream left to right and emits an output every so often; which word an
 // output comes from depends on every rejection before it.  Both samplers are finite-state transducers over the word
 // stream, so the dependence is a prefix scan of state maps:
-//   pass 1 (k_*_map)   each thread owns a chunk of L = 64 consecutive words (reached by the O(log k) LCG jump) and
+//   pass 1 (k_*_map)   each warp owns a chunk of ZL = 2048 consecutive words (reached by the O(log k) LCG jump) and
 //                      computes, for every state the chunk could be entered in, the exit state and the number of
-//                      outputs emitted -- one simulation from the start state plus short ones that merge into it;
-//   pass 2 (k_scan_maps) one CTA composes the chunk maps in stream order -> true entry state and output offset per chunk;
-//   pass 3 (k_*_emit)  each thread re-runs its chunk from the true entry state and writes its outputs at their offset.
+//                      outputs emitted -- one walk from the start state plus walks from the other entry states that
+//                      last until they meet it (usually within the first 32 words);
+//   pass 2 (k_scan_*)  the chunk maps are composed in stream order (three-level scan) -> true entry state and output
+//                      offset per chunk;
+//   pass 3 (k_*_emit)  each warp re-walks its chunk from the true entry state and writes the values.
+// A warp walks a chunk 32 words per step, lane l taking word 32*step + l (its LCG strides by 32), so the values of a
+// step go to consecutive addresses.  Every lane first evaluates its word as if entered in S; when the whole step
+// fast-accepts (68 % of steps) that is the answer, otherwise the few lanes entered mid-draw are resolved in stream
+// order by a warp-uniform walk over the non-S exits (resolve_walk).
 // Element i of the result is therefore exactly the i-th value the host generator would return, independent of launch
 // geometry.  Ziggurat states: S (fresh word), W (wedge test pending on the previous word), T1/T2 (tail loop, first /
 // second uniform of a pair) with the sign bit of the word that entered the tail.
@@ -19,7 +25,7 @@
 
 namespace nb {
 
-constexpr int ZL = 64;             // words per chunk
+constexpr int ZL = 2048;           // words per chunk (one warp, ZL / 32 steps)
 constexpr int ZS = 0, ZW = 1, ZT1 = 2, ZT2 = 3;
 constexpr int ZSIGN = 4;           // tail sign bit (set = negative)
 constexpr int ZINHERIT = 8;        // tail sign comes from the entry state (tail entered before this chunk)
@@ -54,8 +60,15 @@ __device__ __forceinline__ bool zig_step(int& st, uint64_t w, uint64_t prev, dou
     if (r & 1) x = -x;
     st = ZS;
     const double lhs = __dadd_rn(__dmul_rn(T.fi[idx - 1] - T.fi[idx], u53(w)), T.fi[idx]);
-    const double rhs = exp(__dmul_rn(__dmul_rn(-0.5, x), x));
-    if (lhs < rhs) { val = x; return true; }
+    const double arg = __dmul_rn(__dmul_rn(-0.5, x), x);          // in [-6.7, 0]
+    // the single-precision exponential (relative error < 1e-5 on this range) decides all but ~1e-4 of the tests;
+    // the others are settled by the double-precision one, so the decision is always the double-precision decision
+    const double approx = (double)__expf((float)arg);
+    bool accept;
+    if (lhs < approx * (1.0 - 1e-4)) accept = true;
+    else if (lhs > approx * (1.0 + 1e-4)) accept = false;
+    else accept = lhs < exp(arg);
+    if (accept) { val = x; return true; }
     return false;
   }
   if (base == ZT1) { st = (st & ~3) | ZT2; return false; }
@@ -72,14 +85,18 @@ __device__ __forceinline__ bool zig_step(int& st, uint64_t w, uint64_t prev, dou
   return false;
 }
 
-// chunk map: byte b (b = entry base state 0..3) of the low word = exit code (base | sign | inherit), byte b of the
-// high word = outputs emitted when entered in b
-__device__ __forceinline__ uint64_t pack_map(const int exits[4], const int cnt[4]) {
-  uint32_t lo = 0, hi = 0;
+// chunk map: byte b (b = entry base state 0..3) of .x = exit code (base | sign | inherit), 16-bit field b of .y =
+// outputs emitted when entered in b
+typedef ulonglong2 ChunkMap;
+
+__device__ __forceinline__ ChunkMap pack_map(const int exits[4], const int cnt[4]) {
+  uint64_t lo = 0, hi = 0;
 #pragma unroll
-  for (int b = 0; b < 4; ++b) { lo |= (uint32_t)(exits[b] & 0xff) << (8 * b); hi |= (uint32_t)(cnt[b] & 0xff) << (8 * b); }
-  return ((uint64_t)hi << 32) | lo;
+  for (int b = 0; b < 4; ++b) { lo |= (uint64_t)(exits[b] & 0xff) << (8 * b); hi |= (uint64_t)(cnt[b] & 0xffff) << (16 * b); }
+  return make_ulonglong2(lo, hi);
 }
+__device__ __forceinline__ int map_exit(const ChunkMap& mp, int base) { return (int)((mp.x >> (8 * base)) & 0xff); }
+__device__ __forceinline__ long long map_count(const ChunkMap& mp, int base) { return (long long)((mp.y >> (16 * base)) & 0xffff); }
 
 __device__ __forceinline__ void load_tables(uint64_t* ski, double* swi, double* sfi) {
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -90,63 +107,112 @@ __device__ __forceinline__ void load_tables(uint64_t* ski, double* swi, double* 
   __syncthreads();
 }
 
+// Given every lane's exit when entered in S (st_s, with not_s = ballot(st_s != S)) and the state `carry` lane 0 is
+// entered in, re-evaluates the lanes that are entered mid-draw (emit / val are overwritten for those) and returns
+// the state after lane 31.
+__device__ __forceinline__ int resolve_walk(int carry, unsigned not_s, int st_s, uint64_t w, uint64_t prev, int lane,
+                                            bool& emit, double& val, const ZigTables& T) {
+  const unsigned full = 0xffffffffu;
+  int cur = carry, l = 0;
+  while (l < 32) {
+    if ((cur & 3) == ZS) {
+      const unsigned rest = not_s & (full << l);
+      if (rest == 0u) break;
+      const int l2 = __ffs(rest) - 1;
+      cur = __shfl_sync(full, st_s, l2);
+      l = l2 + 1;
+    } else {
+      int st2 = cur;
+      if (lane == l) {
+        double v2 = 0.0;
+        emit = zig_step(st2, w, prev, v2, T);
+        val = v2;
+      }
+      cur = __shfl_sync(full, st2, l);
+      l = l + 1;
+    }
+  }
+  return cur;
+}
+
+// per-lane LCG of a warp that walks chunk c: `s` gives lane's first word, (m32, p32) strides by 32 words;
+// returns the chunk's start state (whose output is the word before the chunk)
+__device__ __forceinline__ u128 lane_stream(u128 s_start, u128 inc, int lane, u128& s, u128& m32, u128& p32) {
+  const u128 a = NB_PCG_MULT;
+  u128 m, p;
+  lcg_advance(a, inc, (uint64_t)lane + 1, m, p);
+  lcg_advance(a, inc, 32, m32, p32);
+  s = s_start * m + p;
+  return s_start;
+}
+
 __global__ void __launch_bounds__(128)
 k_zig_map(int64_t nchunks, uint64_t s_hi, uint64_t s_lo, uint64_t i_hi, uint64_t i_lo,
-          uint64_t* __restrict__ maps, ulonglong2* __restrict__ lcg) {
+          ChunkMap* __restrict__ maps, ulonglong2* __restrict__ lcg) {
   __shared__ uint64_t ski[256];
   __shared__ double swi[256], sfi[256];
   load_tables(ski, swi, sfi);
   const ZigTables T{ski, swi, sfi};
-  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int64_t c = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
   if (c >= nchunks) return;
   const u128 a = NB_PCG_MULT, inc = make128(i_hi, i_lo);
   u128 m, p;
   lcg_advance(a, inc, (uint64_t)c * ZL, m, p);
-  const u128 s_start = make128(s_hi, s_lo) * m + p;      // state whose output is word c*L - 1
-  lcg[c] = make_ulonglong2((uint64_t)s_start, (uint64_t)(s_start >> 64));
-  const uint64_t prev0 = xsl_rr(s_start);
-  // the path entered in S
-  uint64_t emit_mask = 0, s_mask = 0;
-  int st = ZS;
-  {
-    u128 s = s_start;
-    uint64_t prev = prev0;
-#pragma unroll 4
-    for (int j = 0; j < ZL; ++j) {
-      if (st == ZS) s_mask |= 1ull << j;
-      s = s * a + inc;
-      const uint64_t w = xsl_rr(s);
-      double v;
-      if (zig_step(st, w, prev, v, T)) emit_mask |= 1ull << j;
-      prev = w;
-    }
-  }
-  int exits[4], cnt[4];
-  exits[ZS] = st;
-  cnt[ZS] = __popcll(emit_mask);
-  // the paths entered mid-draw: simulate until they meet the S path in state S
-  for (int b = ZW; b <= ZT2; ++b) {
-    int sb = (b == ZW) ? ZW : (b | ZINHERIT);
-    int n = 0;
-    bool merged = false;
-    u128 s = s_start;
-    uint64_t prev = prev0;
-    for (int j = 0; j < ZL; ++j) {
-      if (sb == ZS && ((s_mask >> j) & 1)) {
-        n += __popcll(emit_mask >> j);
-        merged = true;
-        break;
+  const u128 s_start = make128(s_hi, s_lo) * m + p;      // state whose output is word c*ZL - 1
+  if (lane == 0) lcg[c] = make_ulonglong2((uint64_t)s_start, (uint64_t)(s_start >> 64));
+  u128 s, m32, p32;
+  lane_stream(s_start, inc, lane, s, m32, p32);
+  uint64_t last_prev = xsl_rr(s_start);
+  const unsigned full = 0xffffffffu;
+  int carry = ZS, cnt = 0;
+  int alt_carry[3] = {ZW, ZT1 | ZINHERIT, ZT2 | ZINHERIT};
+  int alt_cnt[3] = {0, 0, 0};
+  bool alt_live[3] = {true, true, true};
+  bool any_live = true;
+  for (int it = 0; it < ZL / 32; ++it) {
+    const uint64_t w = xsl_rr(s);
+    s = s * m32 + p32;
+    uint64_t prev = __shfl_up_sync(full, w, 1);
+    if (lane == 0) prev = last_prev;
+    last_prev = __shfl_sync(full, w, 31);
+    int st_s = ZS;
+    double val_s = 0.0;
+    const bool emit_s = zig_step(st_s, w, prev, val_s, T);
+    const unsigned not_s = __ballot_sync(full, st_s != ZS);
+    bool emit = emit_s;
+    double val = val_s;
+    if (not_s != 0u || carry != ZS) carry = resolve_walk(carry, not_s, st_s, w, prev, lane, emit, val, T);
+    cnt += __popc(__ballot_sync(full, emit));
+    if (any_live) {
+      any_live = false;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (!alt_live[k]) continue;
+        bool e2 = emit_s;
+        double v2 = val_s;
+        alt_carry[k] = resolve_walk(alt_carry[k], not_s, st_s, w, prev, lane, e2, v2, T);
+        alt_cnt[k] += __popc(__ballot_sync(full, e2));
+        if (alt_carry[k] == carry) {       // same state after this step: the rest of the chunk is the S-entry walk
+          alt_live[k] = false;
+          alt_cnt[k] -= cnt;               // becomes (emitted so far) - (S-entry walk emitted so far)
+        } else {
+          any_live = true;
+        }
       }
-      s = s * a + inc;
-      const uint64_t w = xsl_rr(s);
-      double v;
-      if (zig_step(sb, w, prev, v, T)) ++n;
-      prev = w;
     }
-    exits[b] = merged ? st : sb;
-    cnt[b] = n;
   }
-  maps[c] = pack_map(exits, cnt);
+  if (lane == 0) {
+    int exits[4], counts[4];
+    exits[ZS] = carry;
+    counts[ZS] = cnt;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      exits[k + 1] = alt_live[k] ? alt_carry[k] : carry;
+      counts[k + 1] = alt_live[k] ? alt_cnt[k] : alt_cnt[k] + cnt;
+    }
+    maps[c] = pack_map(exits, counts);
+  }
 }
 
 // Composes the chunk maps in stream order (one CTA).  entry[c] = state code chunk c is entered in (base | sign),
@@ -162,35 +228,111 @@ __device__ __forceinline__ int apply_exit(int cur, int exit_code) {
   return exit_code & 7;
 }
 
-constexpr int SCAN_T = 512;
+// The composition runs on three levels so that no thread walks more than SCAN_PER chunks or SCAN_T partial maps:
+//   k_scan_groups   one CTA per group of SCAN_T * SCAN_PER chunks: each thread composes SCAN_PER chunk maps, thread 0
+//                   composes the SCAN_T partial maps -> one map per group;
+//   k_scan_top      one thread walks the group maps in stream order -> entry state and offset of every group;
+//   k_scan_apply    one CTA per group again: partial maps as before, thread 0 turns them into the entry of every
+//                   thread's first chunk, every thread walks its chunks writing entry[c] and offs[c].
+constexpr int SCAN_T = 256;
+constexpr int SCAN_PER = 16;
+constexpr int SCAN_GROUP = SCAN_T * SCAN_PER;
+
+__device__ __forceinline__ void range_identity(RangeMap& r) {
+#pragma unroll
+  for (int b = 0; b < 4; ++b) { r.ex[b] = (b >= ZT1) ? (b | ZINHERIT) : b; r.cnt[b] = 0; }
+}
+
+__device__ __forceinline__ void range_push(RangeMap& r, const ChunkMap& mp) {
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    const int cur = r.ex[b];
+    const int base = cur & 3;
+    r.cnt[b] += map_count(mp, base);
+    r.ex[b] = apply_exit(cur, map_exit(mp, base));
+  }
+}
+
+// r then g (both range maps)
+__device__ __forceinline__ void range_then(RangeMap& r, const RangeMap& g) {
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    const int cur = r.ex[b];
+    const int base = cur & 3;
+    r.cnt[b] += g.cnt[base];
+    r.ex[b] = apply_exit(cur, g.ex[base]);
+  }
+}
+
+__device__ __forceinline__ void thread_range(int64_t nchunks, const ChunkMap* __restrict__ maps, int64_t& lo,
+                                             int64_t& hi, RangeMap& r) {
+  lo = min(nchunks, (int64_t)blockIdx.x * SCAN_GROUP + (int64_t)threadIdx.x * SCAN_PER);
+  hi = min(nchunks, lo + SCAN_PER);
+  range_identity(r);
+  for (int64_t c = lo; c < hi; ++c) range_push(r, maps[c]);
+}
 
 __global__ void __launch_bounds__(SCAN_T)
-k_scan_maps(int64_t nchunks, const uint64_t* __restrict__ maps, unsigned char* __restrict__ entry,
-            long long* __restrict__ offs, long long* __restrict__ header) {
+k_scan_groups(int64_t nchunks, const ChunkMap* __restrict__ maps, RangeMap* __restrict__ group_maps) {
+  __shared__ RangeMap rm[SCAN_T];
+  int64_t lo, hi;
+  RangeMap r;
+  thread_range(nchunks, maps, lo, hi, r);
+  rm[threadIdx.x] = r;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    RangeMap g;
+    range_identity(g);
+    for (int i = 0; i < SCAN_T; ++i) range_then(g, rm[i]);
+    group_maps[blockIdx.x] = g;
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_T)
+k_scan_top(int ngroups, const RangeMap* __restrict__ group_maps, int* __restrict__ group_state,
+           long long* __restrict__ group_off, long long* __restrict__ header) {
+  __shared__ RangeMap tile[SCAN_T];
+  __shared__ int cur_s;
+  __shared__ long long off_s;
+  if (threadIdx.x == 0) { cur_s = ZS; off_s = 0; }
+  for (int g0 = 0; g0 < ngroups; g0 += SCAN_T) {
+    const int g = g0 + threadIdx.x;
+    if (g < ngroups) tile[threadIdx.x] = group_maps[g];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int cur = cur_s;
+      long long off = off_s;
+      const int m = min(SCAN_T, ngroups - g0);
+      for (int i = 0; i < m; ++i) {
+        group_state[g0 + i] = cur;
+        group_off[g0 + i] = off;
+        const int base = cur & 3;
+        off += tile[i].cnt[base];
+        cur = apply_exit(cur, tile[i].ex[base]) & 7;
+      }
+      cur_s = cur;
+      off_s = off;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { header[0] = off_s; header[1] = cur_s; }
+}
+
+__global__ void __launch_bounds__(SCAN_T)
+k_scan_apply(int64_t nchunks, const ChunkMap* __restrict__ maps, const int* __restrict__ group_state,
+             const long long* __restrict__ group_off, unsigned char* __restrict__ entry,
+             long long* __restrict__ offs) {
   __shared__ RangeMap rm[SCAN_T];
   __shared__ int ent_state[SCAN_T];
   __shared__ long long ent_off[SCAN_T];
-  const int t = threadIdx.x;
-  const int64_t q = (nchunks + SCAN_T - 1) / SCAN_T;
-  const int64_t lo = min(nchunks, (int64_t)t * q), hi = min(nchunks, lo + q);
+  int64_t lo, hi;
   RangeMap r;
-#pragma unroll
-  for (int b = 0; b < 4; ++b) { r.ex[b] = (b >= ZT1) ? (b | ZINHERIT) : b; r.cnt[b] = 0; }
-  for (int64_t c = lo; c < hi; ++c) {
-    const uint64_t mp = maps[c];
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int cur = r.ex[b];
-      const int base = cur & 3;
-      r.cnt[b] += (long long)((mp >> (32 + 8 * base)) & 0xff);
-      r.ex[b] = apply_exit(cur, (int)((mp >> (8 * base)) & 0xff));
-    }
-  }
-  rm[t] = r;
+  thread_range(nchunks, maps, lo, hi, r);
+  rm[threadIdx.x] = r;
   __syncthreads();
-  if (t == 0) {
-    int cur = ZS;
-    long long off = 0;
+  if (threadIdx.x == 0) {
+    int cur = group_state[blockIdx.x];
+    long long off = group_off[blockIdx.x];
     for (int i = 0; i < SCAN_T; ++i) {
       ent_state[i] = cur;
       ent_off[i] = off;
@@ -198,22 +340,21 @@ k_scan_maps(int64_t nchunks, const uint64_t* __restrict__ maps, unsigned char* _
       off += rm[i].cnt[base];
       cur = apply_exit(cur, rm[i].ex[base]) & 7;
     }
-    header[0] = off;
-    header[1] = cur;
   }
   __syncthreads();
-  int cur = ent_state[t];
-  long long off = ent_off[t];
+  int cur = ent_state[threadIdx.x];
+  long long off = ent_off[threadIdx.x];
   for (int64_t c = lo; c < hi; ++c) {
-    const uint64_t mp = maps[c];
+    const ChunkMap mp = maps[c];
     entry[c] = (unsigned char)cur;
     offs[c] = off;
     const int base = cur & 3;
-    off += (long long)((mp >> (32 + 8 * base)) & 0xff);
-    cur = apply_exit(cur, (int)((mp >> (8 * base)) & 0xff)) & 7;
+    off += map_count(mp, base);
+    cur = apply_exit(cur, map_exit(mp, base)) & 7;
   }
 }
 
+// Pass 3: the warp of chunk c walks it from its true entry state and writes the values at their offsets.
 __global__ void __launch_bounds__(128)
 k_zig_emit(int64_t nchunks, int64_t n, uint64_t i_hi, uint64_t i_lo, const ulonglong2* __restrict__ lcg,
            const unsigned char* __restrict__ entry, const long long* __restrict__ offs,
@@ -222,24 +363,34 @@ k_zig_emit(int64_t nchunks, int64_t n, uint64_t i_hi, uint64_t i_lo, const ulong
   __shared__ double swi[256], sfi[256];
   load_tables(ski, swi, sfi);
   const ZigTables T{ski, swi, sfi};
-  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int64_t c = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
   if (c >= nchunks) return;
   long long off = offs[c];
   if (off >= n) return;
-  const u128 a = NB_PCG_MULT, inc = make128(i_hi, i_lo);
+  int carry = entry[c];
   const ulonglong2 ls = lcg[c];
-  u128 s = make128(ls.y, ls.x);
-  uint64_t prev = xsl_rr(s);
-  int st = entry[c];
-  for (int j = 0; j < ZL; ++j) {
-    s = s * a + inc;
+  const u128 s_start = make128(ls.y, ls.x);
+  u128 s, m32, p32;
+  lane_stream(s_start, make128(i_hi, i_lo), lane, s, m32, p32);
+  uint64_t last_prev = xsl_rr(s_start);           // the word before this chunk
+  const unsigned full = 0xffffffffu, lt = (1u << lane) - 1u;
+  for (int it = 0; it < ZL / 32; ++it) {
     const uint64_t w = xsl_rr(s);
-    double v;
-    if (zig_step(st, w, prev, v, T)) {
-      if (off < n) out[off] = affine ? __dadd_rn(loc, __dmul_rn(scale, v)) : v;
-      ++off;
-    }
-    prev = w;
+    s = s * m32 + p32;
+    uint64_t prev = __shfl_up_sync(full, w, 1);
+    if (lane == 0) prev = last_prev;
+    last_prev = __shfl_sync(full, w, 31);
+    int st_s = ZS;
+    double val = 0.0;
+    bool emit = zig_step(st_s, w, prev, val, T);
+    const unsigned not_s = __ballot_sync(full, st_s != ZS);
+    if (not_s != 0u || carry != ZS) carry = resolve_walk(carry, not_s, st_s, w, prev, lane, emit, val, T);
+    const unsigned em = __ballot_sync(full, emit);
+    const long long at = off + __popc(em & lt);
+    if (emit && at < n) out[at] = affine ? __dadd_rn(loc, __dmul_rn(scale, val)) : val;
+    off += __popc(em);
+    if (off >= n) break;
   }
 }
 
@@ -259,19 +410,22 @@ __device__ __forceinline__ bool lemire64(uint64_t x, uint64_t rng_excl, uint64_t
 template <int MODE>
 __global__ void __launch_bounds__(128)
 k_int_map(int64_t nchunks, uint64_t s_hi, uint64_t s_lo, uint64_t i_hi, uint64_t i_lo, uint64_t rng_excl,
-          uint64_t threshold, uint64_t* __restrict__ maps, ulonglong2* __restrict__ lcg) {
-  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+          uint64_t threshold, ChunkMap* __restrict__ maps, ulonglong2* __restrict__ lcg) {
+  const int lane = threadIdx.x & 31;
+  const int64_t c = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
   if (c >= nchunks) return;
   const u128 a = NB_PCG_MULT, inc = make128(i_hi, i_lo);
   u128 m, p;
   lcg_advance(a, inc, (uint64_t)c * ZL, m, p);
-  u128 s = make128(s_hi, s_lo) * m + p;
-  lcg[c] = make_ulonglong2((uint64_t)s, (uint64_t)(s >> 64));
+  const u128 s_start = make128(s_hi, s_lo) * m + p;
+  if (lane == 0) lcg[c] = make_ulonglong2((uint64_t)s_start, (uint64_t)(s_start >> 64));
+  u128 s, m32, p32;
+  lane_stream(s_start, inc, lane, s, m32, p32);
   int n = 0;
 #pragma unroll 4
-  for (int j = 0; j < ZL; ++j) {
-    s = s * a + inc;
+  for (int it = 0; it < ZL / 32; ++it) {
     const uint64_t w = xsl_rr(s);
+    s = s * m32 + p32;
     uint64_t v;
     if (MODE == 0) {
       n += lemire32((uint32_t)w, (uint32_t)rng_excl, (uint32_t)threshold, v) ? 1 : 0;
@@ -280,8 +434,12 @@ k_int_map(int64_t nchunks, uint64_t s_hi, uint64_t s_lo, uint64_t i_hi, uint64_t
       n += lemire64(w, rng_excl, threshold, v) ? 1 : 0;
     }
   }
-  int exits[4] = {ZS, ZS, ZS, ZS}, cnt[4] = {n, n, n, n};
-  maps[c] = pack_map(exits, cnt);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if (lane == 0) {
+    int exits[4] = {ZS, ZS, ZS, ZS}, cnt[4] = {n, n, n, n};
+    maps[c] = pack_map(exits, cnt);
+  }
 }
 
 template <int MODE>
@@ -289,32 +447,36 @@ __global__ void __launch_bounds__(128)
 k_int_emit(int64_t nchunks, int64_t n, uint64_t i_hi, uint64_t i_lo, const ulonglong2* __restrict__ lcg,
            const long long* __restrict__ offs, uint64_t rng_excl, uint64_t threshold, uint64_t low,
            long long* __restrict__ out) {
-  const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int64_t c = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
   if (c >= nchunks) return;
   long long off = offs[c];
   if (off >= n) return;
-  const u128 a = NB_PCG_MULT, inc = make128(i_hi, i_lo);
   const ulonglong2 ls = lcg[c];
-  u128 s = make128(ls.y, ls.x);
-  for (int j = 0; j < ZL; ++j) {
-    s = s * a + inc;
+  u128 s, m32, p32;
+  lane_stream(make128(ls.y, ls.x), make128(i_hi, i_lo), lane, s, m32, p32);
+  const unsigned full = 0xffffffffu, lt = (1u << lane) - 1u;
+  for (int it = 0; it < ZL / 32; ++it) {
     const uint64_t w = xsl_rr(s);
-    uint64_t v;
+    s = s * m32 + p32;
     if (MODE == 0) {
-      if (lemire32((uint32_t)w, (uint32_t)rng_excl, (uint32_t)threshold, v)) {
-        if (off < n) out[off] = (long long)(low + v);
-        ++off;
-      }
-      if (lemire32((uint32_t)(w >> 32), (uint32_t)rng_excl, (uint32_t)threshold, v)) {
-        if (off < n) out[off] = (long long)(low + v);
-        ++off;
-      }
+      uint64_t v0, v1;
+      const bool a0 = lemire32((uint32_t)w, (uint32_t)rng_excl, (uint32_t)threshold, v0);
+      const bool a1 = lemire32((uint32_t)(w >> 32), (uint32_t)rng_excl, (uint32_t)threshold, v1);
+      const unsigned b0 = __ballot_sync(full, a0), b1 = __ballot_sync(full, a1);
+      const long long at = off + __popc(b0 & lt) + __popc(b1 & lt);
+      if (a0 && at < n) out[at] = (long long)(low + v0);
+      if (a1 && at + (a0 ? 1 : 0) < n) out[at + (a0 ? 1 : 0)] = (long long)(low + v1);
+      off += __popc(b0) + __popc(b1);
     } else {
-      if (lemire64(w, rng_excl, threshold, v)) {
-        if (off < n) out[off] = (long long)(low + v);
-        ++off;
-      }
+      uint64_t v;
+      const bool ok = lemire64(w, rng_excl, threshold, v);
+      const unsigned b = __ballot_sync(full, ok);
+      const long long at = off + __popc(b & lt);
+      if (ok && at < n) out[at] = (long long)(low + v);
+      off += __popc(b);
     }
+    if (off >= n) break;
   }
 }
 
@@ -355,25 +517,49 @@ k_int_direct(int64_t n, int kind, uint64_t s_hi, uint64_t s_lo, uint64_t i_hi, u
 
 struct ScanScratch {
   long long* header;       // [0] outputs produced, [1] final state
-  uint64_t* maps;
+  ChunkMap* maps;
   ulonglong2* lcg;
   long long* offs;
   unsigned char* entry;
+  RangeMap* group_maps;
+  long long* group_off;
+  int* group_state;
+  int ngroups;
 };
 
+static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+static inline int groups_for(int64_t nchunks) { return (int)((nchunks + SCAN_GROUP - 1) / SCAN_GROUP); }
+
 static size_t scan_scratch_bytes(int64_t nchunks) {
-  return 256 + (size_t)nchunks * (8 + 16 + 8) + (((size_t)nchunks + 255) & ~(size_t)255);
+  const size_t g = (size_t)groups_for(nchunks);
+  return 256 + (size_t)nchunks * (16 + 16 + 8) + up256((size_t)nchunks) + up256(g * sizeof(RangeMap)) +
+         up256(g * 8) + up256(g * 4);
 }
 
 static ScanScratch carve(void* scratch, int64_t nchunks) {
   ScanScratch s;
   unsigned char* p = (unsigned char*)scratch;
+  s.ngroups = groups_for(nchunks);
   s.header = (long long*)p; p += 256;
   s.lcg = (ulonglong2*)p; p += (size_t)nchunks * 16;
-  s.maps = (uint64_t*)p; p += (size_t)nchunks * 8;
+  s.maps = (ChunkMap*)p; p += (size_t)nchunks * 16;
   s.offs = (long long*)p; p += (size_t)nchunks * 8;
-  s.entry = p;
+  s.entry = p; p += up256((size_t)nchunks);
+  s.group_maps = (RangeMap*)p; p += up256((size_t)s.ngroups * sizeof(RangeMap));
+  s.group_off = (long long*)p; p += up256((size_t)s.ngroups * 8);
+  s.group_state = (int*)p;
   return s;
+}
+
+// maps -> entry state and output offset of every chunk, total in header[0]
+static int run_scan(const ScanScratch& sc, int64_t nchunks, cudaStream_t st) {
+  k_scan_groups<<<sc.ngroups, SCAN_T, 0, st>>>(nchunks, sc.maps, sc.group_maps);
+  NB_LAUNCH_CHECK();
+  k_scan_top<<<1, SCAN_T, 0, st>>>(sc.ngroups, sc.group_maps, sc.group_state, sc.group_off, sc.header);
+  NB_LAUNCH_CHECK();
+  k_scan_apply<<<sc.ngroups, SCAN_T, 0, st>>>(nchunks, sc.maps, sc.group_state, sc.group_off, sc.entry, sc.offs);
+  NB_LAUNCH_CHECK();
+  return 0;
 }
 
 // words to scan so that at least n normals come out: the ziggurat takes the first word of a draw 98.8 % of the time
@@ -436,11 +622,10 @@ extern "C" int nb_pcg64_normal(int device, int64_t n, const uint64_t* state_hi_l
   NB_REQUIRE(scratch_d != nullptr && scratch_bytes >= (int64_t)scan_scratch_bytes(nchunks),
              "nb_pcg64_normal: scratch smaller than nb_pcg64_normal_scratch_bytes(n)");
   ScanScratch sc = carve(scratch_d, nchunks);
-  const int grid = (int)((nchunks + 127) / 128);
+  const int grid = (int)((nchunks + 3) / 4);
   k_zig_map<<<grid, 128, 0, st>>>(nchunks, state_hi_lo[0], state_hi_lo[1], inc_hi_lo[0], inc_hi_lo[1], sc.maps, sc.lcg);
   NB_LAUNCH_CHECK();
-  k_scan_maps<<<1, SCAN_T, 0, st>>>(nchunks, sc.maps, sc.entry, sc.offs, sc.header);
-  NB_LAUNCH_CHECK();
+  if (int rc = run_scan(sc, nchunks, st)) return rc;
   k_zig_emit<<<grid, 128, 0, st>>>(nchunks, n, inc_hi_lo[0], inc_hi_lo[1], sc.lcg, sc.entry, sc.offs, loc, scale,
                                    standard ? 0 : 1, out_d);
   NB_LAUNCH_CHECK();
@@ -474,7 +659,7 @@ extern "C" int nb_pcg64_integers(int device, int64_t n, const uint64_t* state_hi
   NB_REQUIRE(scratch_d != nullptr && scratch_bytes >= (int64_t)scan_scratch_bytes(pl.nchunks),
              "nb_pcg64_integers: scratch smaller than nb_pcg64_integers_scratch_bytes(n, rng)");
   ScanScratch sc = carve(scratch_d, pl.nchunks);
-  const int grid = (int)((pl.nchunks + 127) / 128);
+  const int grid = (int)((pl.nchunks + 3) / 4);
   if (pl.kind == 5) {
     k_int_map<0><<<grid, 128, 0, st>>>(pl.nchunks, state_hi_lo[0], state_hi_lo[1], inc_hi_lo[0], inc_hi_lo[1],
                                        pl.rng_excl, pl.threshold, sc.maps, sc.lcg);
@@ -483,8 +668,7 @@ extern "C" int nb_pcg64_integers(int device, int64_t n, const uint64_t* state_hi
                                        pl.rng_excl, pl.threshold, sc.maps, sc.lcg);
   }
   NB_LAUNCH_CHECK();
-  k_scan_maps<<<1, SCAN_T, 0, st>>>(pl.nchunks, sc.maps, sc.entry, sc.offs, sc.header);
-  NB_LAUNCH_CHECK();
+  if (int rc = run_scan(sc, pl.nchunks, st)) return rc;
   if (pl.kind == 5) {
     k_int_emit<0><<<grid, 128, 0, st>>>(pl.nchunks, n, inc_hi_lo[0], inc_hi_lo[1], sc.lcg, sc.offs, pl.rng_excl,
                                         pl.threshold, (uint64_t)low, (long long*)out_d);

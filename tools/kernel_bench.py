@@ -145,6 +145,22 @@ def main():
     S = dv.from_numpy(S.T @ S + np.eye(257), 0)
     add("inv 257 x 257", "numpy_kernel.py:471", timeit(lambda: K.inv(S), reps=5))
 
+    # factorisations: one block of a tall-skinny QR, and the p x p ends
+    nq = (n * 4) // 256
+    Xq = big(nq * 256)
+    Xq = dv.DeviceBlock(Xq.t.view(nq, 256))
+    pert = dv.from_numpy(rng.standard_normal((256,)), 0)
+    Xq = K.bop("add", Xq, dv.DeviceBlock(pert.t.view(1, 256)), False, False, {})     # tiled draws alone are rank deficient
+    qr_flops = 2.0 * nq * 256 * 257 + 2.0 * nq * 256 * 256        # two Gram passes (symmetric) + one n x d x d product
+    add("qr mode='r' (CholeskyQR2 + Householder signs), %d x 256" % nq, "numpy_kernel.py:455-461 / linalg.py:55-103",
+        timeit(lambda: K.qr(Xq, mode="r"), reps=2, warm=1), 8 * nq * 256, flops=qr_flops)
+    add("qr mode='reduced', %d x 256" % nq, "numpy_kernel.py:455-461 / linalg.py:130-208",
+        timeit(lambda: K.qr(Xq, mode="reduced"), reps=2, warm=1), 8 * nq * 256, flops=qr_flops + 2.0 * nq * 256 * 256)
+    del Xq
+    Ssp = dv.from_numpy(np.asarray(dv.to_numpy(S))[:256, :256].copy(), 0)
+    add("cholesky 256 x 256", "numpy_kernel.py:463-464", timeit(lambda: K.cholesky(Ssp), reps=5))
+    add("svd 256 x 256 (one-sided Jacobi)", "numpy_kernel.py:466-469", timeit(lambda: K.svd(Ssp), reps=3))
+
     # block RNG in HBM: same values as the host generator, which is timed on 10^7 draws beside it
     import time as _t
     from numpy.random import PCG64, Generator
