@@ -333,6 +333,11 @@ k_glm_predict(int family, const double* __restrict__ x, int64_t n, int64_t d, in
 static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 // glm_fused.cu
+bool glm_regs_applicable(int64_t d);
+size_t glm_regs_scratch_bytes(int device, int64_t d);
+int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                   const double* beta, int want_hess, double* stats, void* scratch, size_t scratch_bytes,
+                   cudaStream_t st);
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
 int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
@@ -381,6 +386,10 @@ static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
   if (want_hess && d >= 8 && d <= 256) {   // the triangular / single-pass kernels take their partials from the GEMM region
     size_t f = L.off_gemm + align256(fused_scratch_bytes(device, n, d));
     if (f > cur) cur = f;
+  }
+  if (glm_regs_applicable(d)) {             // register-resident single pass (glm_regs.cu) takes its partials from offset 0
+    size_t r = align256(glm_regs_scratch_bytes(device, d));
+    if (r > cur) cur = r;
   }
   L.total = cur;
   return L;
@@ -489,6 +498,8 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
       default: return launch_small_d<NB_GLM_LINEAR>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
     }
   }
+  if (glm_regs_applicable(d))
+    return glm_regs_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, stats_d, sc, L.total, st);
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);
   if (tri_ok && glm_mode() == 1)
     return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, nullptr, true, stats_d, d + 1,

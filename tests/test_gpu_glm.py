@@ -194,6 +194,27 @@ def test_glm_stats_families_and_strides(app, family, ydtype, n, d, ldx):
     assert rel_err(obj, obj0) < STAT_TOL
 
 
+@pytest.mark.parametrize("d", [8, 9, 16, 17, 24, 28, 33, 40, 47, 56, 63, 64])
+@pytest.mark.parametrize("family", ["logistic", "linear", "poisson"])
+def test_register_resident_pass_every_width(app, family, d):
+    """8 <= d <= 64 runs the single-pass register kernel (csrc/glm_regs.cu): every column-block count, widths that
+    are not multiples of 8, a ragged row count, Newton statistics and the gradient-only evaluation of L-BFGS."""
+    from nums_b200 import device as dv, fused
+    n = 20_011 + d
+    ydtype = np.float64 if family == "linear" else np.int64
+    (H, g, obj), (H0, g0, obj0) = raw_stats(n, d, family, ydtype, seed=7)
+    assert rel_err(g, g0) < STAT_TOL and rel_err(H, H0) < STAT_TOL and rel_err(obj, obj0) < STAT_TOL
+    assert np.array_equal(H, H.T)
+    rng = np.random.default_rng(7 + d)          # same draws as raw_stats: gradient-only pass on the same block
+    X = rng.standard_normal((n, d)) / np.sqrt(d)
+    beta = rng.standard_normal(d + 1) * 0.5
+    y = ((rng.random(n) < 0.4) if family == "logistic" else
+         (rng.poisson(1.5, n) if family == "poisson" else rng.standard_normal(n))).astype(ydtype)
+    s = dv.to_numpy(fused.glm_stats(dv.from_numpy(X, 0), dv.from_numpy(y, 0), dv.from_numpy(beta, 0), family, False))
+    p = d + 1
+    assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
+
+
 def test_glm_edge_cases(app):
     """ragged last block, a single row, and an empty row block"""
     from nums_b200.glms import LogisticRegression
