@@ -144,14 +144,14 @@ k_glm_rows(const GlmRowsArgs a) {
   constexpr int RG = NW / WPR;
   constexpr int CW = 64 * NJ;
   extern __shared__ __align__(16) double dyn[];
-  double* s_beta = dyn;                         // d + 1
-  double* s_acc = dyn + ((a.d + 2) & ~(int64_t)1);  // 2 * WPR * CW  (g then u), then 4 scalars
+  double* s_beta = dyn;                         // WPR * CW: beta[0..d) then zeros (so no column guard is needed)
+  double* s_acc = dyn + WPR * CW;               // 2 * WPR * CW  (g then u), then 4 scalars
   __shared__ double s_eta[2][RG][WPR][R];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rg = warp / WPR, wc = warp % WPR;
   const int64_t d = a.d, n = a.n;
-  for (int64_t j = tid; j <= d; j += GLM_THREADS) s_beta[j] = a.beta[j];
+  for (int j = tid; j < WPR * CW; j += GLM_THREADS) s_beta[j] = j < d ? a.beta[j] : 0.0;
   for (int j = tid; j < 2 * WPR * CW + 4; j += GLM_THREADS) s_acc[j] = 0.0;
   __syncthreads();
 
@@ -164,7 +164,7 @@ k_glm_rows(const GlmRowsArgs a) {
 #pragma unroll
     for (int e = 0; e < NE; e++) bet[e] = CV(e) ? s_beta[COL(e)] : 0.0;
   }
-  const double beta0 = s_beta[d];
+  const double beta0 = a.beta[d];
 
   double g[NE], u[HESS ? NE : 1];
 #pragma unroll
@@ -200,20 +200,48 @@ k_glm_rows(const GlmRowsArgs a) {
         for (int e = 0; e < NE; e++) xv[r][e] = (row < n && CV(e)) ? xr[COL(e)] : 0.0;
       }
     }
+    // eta partials: beta comes from shared memory once per column slot and serves all R rows; four independent
+    // sums per row keep the FMA chain short (the kernel runs at one or two warps per scheduler)
     double part[R];
+    {
+      constexpr int NP = R >= 4 ? (HESS ? 1 : 2) : 4;   // fewer partial sums where four rows already give the ILP
+      double ps[R][NP];
 #pragma unroll
-    for (int r = 0; r < R; r++) {
-      double s = 0.0;
+      for (int r = 0; r < R; r++)
 #pragma unroll
-      for (int e = 0; e < NE; e++) {
-        double bv;
-        if constexpr (NJ <= 2) bv = bet[e];
-        else bv = CV(e) ? s_beta[COL(e)] : 0.0;
-        s = fma(xv[r][e], bv, s);
+        for (int k = 0; k < NP; k++) ps[r][k] = 0.0;
+      if constexpr (NJ <= 2) {
+#pragma unroll
+        for (int e = 0; e < NE; e++)
+#pragma unroll
+          for (int r = 0; r < R; r++) ps[r][e & (NP - 1)] = fma(xv[r][e], bet[e], ps[r][e & (NP - 1)]);
+      } else if constexpr (VEC) {
+#pragma unroll
+        for (int j = 0; j < NJ; j++) {
+          const double2 b = *reinterpret_cast<const double2*>(s_beta + COL(2 * j));
+#pragma unroll
+          for (int r = 0; r < R; r++) {
+            ps[r][(2 * j) & (NP - 1)] = fma(xv[r][2 * j], b.x, ps[r][(2 * j) & (NP - 1)]);
+            ps[r][(2 * j + 1) & (NP - 1)] = fma(xv[r][2 * j + 1], b.y, ps[r][(2 * j + 1) & (NP - 1)]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < NE; e++) {
+          const double bv = s_beta[COL(e)];
+#pragma unroll
+          for (int r = 0; r < R; r++) ps[r][e & (NP - 1)] = fma(xv[r][e], bv, ps[r][e & (NP - 1)]);
+        }
       }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      part[r] = s;
+      for (int r = 0; r < R; r++) {
+        double s = ps[r][0];
+        if constexpr (NP >= 2) s += ps[r][1];
+        if constexpr (NP == 4) s += ps[r][2] + ps[r][3];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        part[r] = s;
+      }
     }
     if constexpr (WPR > 1) {
       if (lane == 0) {
@@ -333,8 +361,8 @@ k_glm_predict(int family, const double* __restrict__ x, int64_t n, int64_t d, in
 static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 // glm_fused.cu
-bool glm_regs_applicable(int64_t d);
-size_t glm_regs_scratch_bytes(int device, int64_t d);
+bool glm_regs_applicable(int64_t d, int want_hess);
+size_t glm_regs_scratch_bytes(int device, int64_t d, int want_hess);
 int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                    const double* beta, int want_hess, double* stats, void* scratch, size_t scratch_bytes,
                    cudaStream_t st);
@@ -387,8 +415,8 @@ static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
     size_t f = L.off_gemm + align256(fused_scratch_bytes(device, n, d));
     if (f > cur) cur = f;
   }
-  if (glm_regs_applicable(d)) {             // register-resident single pass (glm_regs.cu) takes its partials from offset 0
-    size_t r = align256(glm_regs_scratch_bytes(device, d));
+  if (glm_regs_applicable(d, want_hess)) {  // register-resident single pass (glm_regs.cu) takes its partials from offset 0
+    size_t r = align256(glm_regs_scratch_bytes(device, d, want_hess));
     if (r > cur) cur = r;
   }
   L.total = cur;
@@ -425,7 +453,7 @@ static int launch_small_d(int device, int64_t d, const double* x, int64_t n, int
 template <int NJ, int WPR, bool VEC, bool HESS>
 static int launch_rows_h(int device, const GlmRowsArgs& a, int max_parts, int* nparts, cudaStream_t st) {
   auto kern = k_glm_rows<NJ, WPR, VEC, HESS>;
-  size_t smem = ((size_t)((a.d + 2) & ~(int64_t)1) + 2 * (size_t)WPR * 64 * NJ + 4) * sizeof(double);
+  size_t smem = (3 * (size_t)WPR * 64 * NJ + 4) * sizeof(double);
   NB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 1;
   NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, GLM_THREADS, smem));
@@ -498,7 +526,7 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
       default: return launch_small_d<NB_GLM_LINEAR>(device, d, x_d, n, ldx, y_d, ydt, beta_d, want_hess, stats_d, parts, L.max_parts, st);
     }
   }
-  if (glm_regs_applicable(d))
+  if (glm_regs_applicable(d, want_hess))
     return glm_regs_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, stats_d, sc, L.total, st);
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);
   if (tri_ok && glm_mode() == 1)

@@ -1,4 +1,5 @@
-// GLM statistics for narrow designs (8 <= d <= 64): one pass over X with everything in registers.
+// GLM statistics for narrow designs: one pass over X with everything in registers (Newton statistics for
+// 8 <= d <= 64, the gradient/objective evaluation of L-BFGS for 8 <= d <= 192).
 //
 // For d <= 64 the whole upper triangle of X^T diag(w) X fits in a warp's registers as 8 x 8 DMMA tiles (36 tiles x 2
 // doubles at d = 64), so no shared-memory staging, no barriers and no second pass are needed: a warp streams four
@@ -34,30 +35,38 @@ struct RegsArgs {
   double* parts;      // per CTA: [dd*dd tiles | g dd | u dd | sum r | sum w | obj]
 };
 
-template <int NB> struct RegsLayout {
+// per-CTA partial (and shared-memory reduction buffer): [DD*DD tiles (Hessian variant only) | g DD | u DD | 3 sums]
+template <int NB, bool HESS> struct RegsLayout {
   static constexpr int DD = 8 * NB;
-  static constexpr int G_OFF = DD * DD, U_OFF = G_OFF + DD, S_OFF = U_OFF + DD, LEN = S_OFF + 3;
+  static constexpr int G_OFF = HESS ? DD * DD : 0, U_OFF = G_OFF + DD, S_OFF = U_OFF + DD, LEN = S_OFF + 3;
 };
 
 // rows per batch = 4 * BATCH: the link function of a batch is evaluated once, lane (q, g) taking row 4 (g % BATCH) + q,
 // and handed to the lanes that need it by shuffles; BATCH is bounded by the registers the x values of a batch take
 template <int NB, bool HESS> struct RegsBatch {
-  static constexpr int value = !HESS ? 8 : (NB <= 4 ? 8 : (NB <= 6 ? 4 : 2));
+  static constexpr int value = !HESS ? (NB <= 8 ? 8 : (NB <= 16 ? 4 : 2)) : (NB <= 4 ? 8 : (NB <= 6 ? 4 : 2));
 };
 
 template <int NB, bool HESS>
 __global__ void __launch_bounds__(RG_THREADS)
 k_glm_regs(RegsArgs a) {
-  using L = RegsLayout<NB>;
+  using L = RegsLayout<NB, HESS>;
   constexpr int DD = L::DD;
   constexpr int BATCH = RegsBatch<NB, HESS>::value;
-  extern __shared__ double red[];                 // L::LEN doubles
+  constexpr bool BET_SMEM = NB > 16;              // wide gradient-only variants keep beta in shared memory
+  extern __shared__ double red[];                 // L::LEN doubles (+ DD of beta)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int q = lane & 3, g = lane >> 2;
   const unsigned full = 0xffffffffu;
-  double bet[NB];
+  double bet[BET_SMEM ? 1 : NB];
+  double* s_bet = red + L::LEN;
+  if constexpr (BET_SMEM) {
+    for (int j = threadIdx.x; j < DD; j += RG_THREADS) s_bet[j] = j < a.d ? a.beta[j] : 0.0;
+    __syncthreads();
+  } else {
 #pragma unroll
-  for (int I = 0; I < NB; ++I) bet[I] = (8 * I + g < a.d) ? a.beta[8 * I + g] : 0.0;
+    for (int I = 0; I < NB; ++I) bet[I] = (8 * I + g < a.d) ? a.beta[8 * I + g] : 0.0;
+  }
   const double b0 = a.beta[a.d];
   double acc[HESS ? NB * (NB + 1) / 2 : 1][2];
 #pragma unroll
@@ -91,7 +100,7 @@ k_glm_regs(RegsArgs a) {
     for (int u = 0; u < BATCH; ++u) {
       double eta = 0.0;
 #pragma unroll
-      for (int I = 0; I < NB; ++I) eta = fma(xv[u][I], bet[I], eta);
+      for (int I = 0; I < NB; ++I) eta = fma(xv[u][I], BET_SMEM ? s_bet[8 * I + g] : bet[BET_SMEM ? 0 : I], eta);
       eta += __shfl_xor_sync(full, eta, 4);
       eta += __shfl_xor_sync(full, eta, 8);
       eta += __shfl_xor_sync(full, eta, 16);
@@ -169,31 +178,31 @@ k_glm_regs(RegsArgs a) {
     __syncthreads();
   }
   double* out = a.parts + (size_t)blockIdx.x * L::LEN;
-  for (int e = threadIdx.x + (HESS ? 0 : L::G_OFF); e < L::LEN; e += RG_THREADS) out[e] = red[e];
+  for (int e = threadIdx.x; e < L::LEN; e += RG_THREADS) out[e] = red[e];
 }
 
 // stats = [H p x p | g p | obj] from the CTA partials, summed in CTA order; H mirrored from its upper triangle
-template <int NB>
+template <int NB, bool HESS>
 __global__ void __launch_bounds__(256)
-k_regs_finish(int64_t d, int nparts, const double* __restrict__ parts, int want_hess, double* __restrict__ stats) {
-  using L = RegsLayout<NB>;
+k_regs_finish(int64_t d, int nparts, const double* __restrict__ parts, double* __restrict__ stats) {
+  using L = RegsLayout<NB, HESS>;
   constexpr int DD = L::DD;
   const int64_t p = d + 1;
   for (int e = blockIdx.x * 256 + threadIdx.x; e < L::LEN; e += gridDim.x * 256) {
     int i = 0, j = 0;
     if (e < L::G_OFF) {
+      // tiles on the diagonal hold both halves (computed with different roundings): only the upper one is used
       i = e / DD; j = e % DD;
-      if (!want_hess || i > j || j >= d || ((i >> 3) > (j >> 3))) continue;
+      if (i > j || j >= d) continue;
     } else if (e < L::S_OFF) {
       if ((e - L::G_OFF) % DD >= d) continue;
-      if (e >= L::U_OFF && !want_hess) continue;
-    } else if (e == L::S_OFF + 1 && !want_hess) {
+      if (e >= L::U_OFF && !HESS) continue;
+    } else if (e == L::S_OFF + 1 && !HESS) {
       continue;
     }
     double s = 0.0;
     for (int c = 0; c < nparts; ++c) s += parts[(size_t)c * L::LEN + e];
     if (e < L::G_OFF) {
-      // tiles on the diagonal hold both halves (computed with different roundings): take the upper one
       stats[i * p + j] = s;
       stats[j * p + i] = s;
     } else if (e < L::U_OFF) {
@@ -212,41 +221,45 @@ k_regs_finish(int64_t d, int nparts, const double* __restrict__ parts, int want_
   }
 }
 
-bool glm_regs_applicable(int64_t d) { return d >= 8 && d <= 64 && !getenv("NUMS_B200_NO_REGS"); }
+// Newton statistics fit a warp's registers up to d = 64; the gradient-only pass (no tiles) up to d = 192
+bool glm_regs_applicable(int64_t d, int want_hess) {
+  return d >= 8 && d <= (want_hess ? 64 : 192) && !getenv("NUMS_B200_NO_REGS");
+}
 
 constexpr int RG_MAX_CTAS_PER_SM = 8;
 static int regs_ctas(int device) { return dev_info(device).sms * RG_MAX_CTAS_PER_SM; }   // scratch is sized for this
 
-size_t glm_regs_scratch_bytes(int device, int64_t d) {
-  const size_t dd = (size_t)((d + 7) / 8) * 8;
-  return (size_t)regs_ctas(device) * (dd * dd + 2 * dd + 3) * sizeof(double);
+static int regs_nb(int64_t d) {        // column blocks of the instantiated variant serving d
+  const int nb = (int)((d + 7) / 8);
+  if (nb <= 8) return nb;
+  if (nb <= 16) return (nb + 1) & ~1;
+  return (nb + 3) & ~3;
 }
 
-template <int NB>
-static int launch_regs(int device, const RegsArgs& a, int want_hess, double* stats, cudaStream_t st) {
-  using L = RegsLayout<NB>;
-  const int64_t rows_per_batch = 4 * (want_hess ? RegsBatch<NB, true>::value : RegsBatch<NB, false>::value);
+size_t glm_regs_scratch_bytes(int device, int64_t d, int want_hess) {
+  const size_t dd = (size_t)regs_nb(d) * 8;
+  return (size_t)regs_ctas(device) * ((want_hess ? dd * dd : 0) + 2 * dd + 3) * sizeof(double);
+}
+
+template <int NB, bool HESS>
+static int launch_regs(int device, const RegsArgs& a, double* stats, cudaStream_t st) {
+  using L = RegsLayout<NB, HESS>;
+  const int64_t rows_per_batch = 4 * RegsBatch<NB, HESS>::value;
   int64_t batches = (a.n + rows_per_batch - 1) / rows_per_batch;
   int64_t want = (batches + RG_WARPS - 1) / RG_WARPS;
-  const size_t smem = (size_t)L::LEN * sizeof(double);
+  const size_t smem = (size_t)(L::LEN + (NB > 16 ? L::DD : 0)) * sizeof(double);
   // one resident wave: as many CTAs per SM as the kernel's registers allow (the narrow variants need the extra
   // warps to keep enough loads in flight)
   int per_sm = 1;
-  if (want_hess) {
-    NB_CHECK(cudaFuncSetAttribute(k_glm_regs<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_glm_regs<NB, true>, RG_THREADS, smem));
-  } else {
-    NB_CHECK(cudaFuncSetAttribute(k_glm_regs<NB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_glm_regs<NB, false>, RG_THREADS, smem));
-  }
+  NB_CHECK(cudaFuncSetAttribute(k_glm_regs<NB, HESS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_glm_regs<NB, HESS>, RG_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
   if (per_sm > RG_MAX_CTAS_PER_SM) per_sm = RG_MAX_CTAS_PER_SM;
   int ctas = dev_info(device).sms * per_sm;
   if (want < ctas) ctas = (int)(want < 1 ? 1 : want);
-  if (want_hess) k_glm_regs<NB, true><<<ctas, RG_THREADS, smem, st>>>(a);
-  else k_glm_regs<NB, false><<<ctas, RG_THREADS, smem, st>>>(a);
+  k_glm_regs<NB, HESS><<<ctas, RG_THREADS, smem, st>>>(a);
   NB_LAUNCH_CHECK();
-  k_regs_finish<NB><<<(L::LEN + 255) / 256, 256, 0, st>>>(a.d, ctas, a.parts, want_hess, stats);
+  k_regs_finish<NB, HESS><<<(L::LEN + 255) / 256, 256, 0, st>>>(a.d, ctas, a.parts, stats);
   NB_LAUNCH_CHECK();
   return 0;
 }
@@ -254,21 +267,22 @@ static int launch_regs(int device, const RegsArgs& a, int want_hess, double* sta
 int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                    const double* beta, int want_hess, double* stats, void* scratch, size_t scratch_bytes,
                    cudaStream_t st) {
-  NB_REQUIRE(glm_regs_applicable(d), "glm_regs_stats: d=%lld outside 8..64", (long long)d);
-  NB_REQUIRE(scratch != nullptr && scratch_bytes >= glm_regs_scratch_bytes(device, d), "glm_regs_stats: scratch too small");
+  NB_REQUIRE(glm_regs_applicable(d, want_hess), "glm_regs_stats: d=%lld outside the register-resident range", (long long)d);
+  NB_REQUIRE(scratch != nullptr && scratch_bytes >= glm_regs_scratch_bytes(device, d, want_hess),
+             "glm_regs_stats: scratch too small");
   RegsArgs a;
   a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.family = family;
   a.parts = (double*)scratch;
-  switch ((d + 7) / 8) {
-    case 1: return launch_regs<1>(device, a, want_hess, stats, st);
-    case 2: return launch_regs<2>(device, a, want_hess, stats, st);
-    case 3: return launch_regs<3>(device, a, want_hess, stats, st);
-    case 4: return launch_regs<4>(device, a, want_hess, stats, st);
-    case 5: return launch_regs<5>(device, a, want_hess, stats, st);
-    case 6: return launch_regs<6>(device, a, want_hess, stats, st);
-    case 7: return launch_regs<7>(device, a, want_hess, stats, st);
-    default: return launch_regs<8>(device, a, want_hess, stats, st);
+  const int nb = regs_nb(d);
+#define RG_CASE(N) case N: return want_hess ? launch_regs<(N <= 8 ? N : 8), true>(device, a, stats, st) \
+                                            : launch_regs<N, false>(device, a, stats, st)
+  switch (nb) {
+    RG_CASE(1); RG_CASE(2); RG_CASE(3); RG_CASE(4); RG_CASE(5); RG_CASE(6); RG_CASE(7); RG_CASE(8);
+    RG_CASE(10); RG_CASE(12); RG_CASE(14); RG_CASE(16); RG_CASE(20); RG_CASE(24);
   }
+#undef RG_CASE
+  set_error("glm_regs_stats: no variant for d=%lld", (long long)d);
+  return 2;
 }
 
 }  // namespace nb

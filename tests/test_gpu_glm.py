@@ -215,6 +215,27 @@ def test_register_resident_pass_every_width(app, family, d):
     assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
 
 
+@pytest.mark.parametrize("d", [65, 72, 96, 100, 128, 130, 161, 192])
+@pytest.mark.parametrize("family", ["logistic", "poisson"])
+def test_register_resident_gradient_pass_wide(app, family, d):
+    """65 <= d <= 192: the gradient/objective evaluation (want_hess=0) still runs in registers (beta in shared memory
+    above 128 columns); the Newton statistics of the same block go through the two-pass kernels."""
+    from nums_b200 import device as dv, fused
+    n = 9_001 + d
+    (H, g, obj), (H0, g0, obj0) = raw_stats(n, d, family, np.int64, seed=11)
+    assert rel_err(g, g0) < STAT_TOL and rel_err(H, H0) < STAT_TOL
+    rng = np.random.default_rng(11 + d)
+    X = rng.standard_normal((n, d)) / np.sqrt(d)
+    beta = rng.standard_normal(d + 1) * 0.5
+    y = ((rng.random(n) < 0.4) if family == "logistic" else rng.poisson(1.5, n)).astype(np.int64)
+    wide = np.zeros((n, d + 3))
+    wide[:, :d] = X
+    for Xd in (dv.from_numpy(X, 0), dv.DeviceBlock(dv.from_numpy(wide, 0).t[:, :d])):
+        s = dv.to_numpy(fused.glm_stats(Xd, dv.from_numpy(y, 0), dv.from_numpy(beta, 0), family, False))
+        p = d + 1
+        assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
+
+
 def test_glm_edge_cases(app):
     """ragged last block, a single row, and an empty row block"""
     from nums_b200.glms import LogisticRegression
