@@ -13,4 +13,18 @@ int gemm_f64(int device, int64_t m, int64_t n, int64_t k, const double* a, int64
 
 size_t gemm_scratch_bytes(int device, int64_t m, int64_t n, int64_t k);
 
+// warp-specialised TMA kernel (matmul_ws.cu)
+struct WsPlan {
+  bool ok;
+  int tiles_m, tiles_n, ntiles, splits, sym;
+  int64_t kchunk;
+  size_t scratch;        // != 0: partial tiles, to be summed by k_gemm_reduce<128,128>
+};
+WsPlan ws_plan(int device, int64_t m, int64_t n, int64_t k, bool sym, bool k_rows);
+bool gemm_ws_aligned(const double* a, int64_t lda, const double* b, int64_t ldb, const double* w, const double* c,
+                     int64_t ldc);
+int gemm_ws_f64(const WsPlan& plan, int64_t m, int64_t n, int64_t k, const double* a, int64_t lda, bool a_mc,
+                const double* b, int64_t ldb, bool b_nc, const double* w, double* c, int64_t ldc, double* part,
+                cudaStream_t st);
+
 }  // namespace nb

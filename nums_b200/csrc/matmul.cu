@@ -723,11 +723,8 @@ k_matmul_i64_thread(int64_t m, int64_t n, int64_t k, const int64_t* __restrict__
 // ------------------------------------------------------------------------------------------------
 // dispatcher
 // ------------------------------------------------------------------------------------------------
-// matmul_ws.cu: warp-specialised, TMA-fed kernel for large m, n
-bool gemm_ws_applicable(int device, int64_t m, int64_t n, int64_t k, const double* a, int64_t lda, const double* b,
-                        int64_t ldb, const double* c, int64_t ldc);
-int gemm_ws_f64(int64_t m, int64_t n, int64_t k, const double* a, int64_t lda, bool a_mc, const double* b, int64_t ldb,
-                bool b_nc, double* c, int64_t ldc, cudaStream_t st);
+// matmul_ws.cu (declared in gemm.cuh): warp-specialised, TMA-fed kernel for large m, n -- direct for square
+// products, split along k for tall-skinny ones
 // glm_fused.cu: warp-specialised upper-triangular X^T diag(w) X for 8 <= d <= 256
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
@@ -745,6 +742,10 @@ size_t gemm_scratch_bytes(int device, int64_t m, int64_t n, int64_t k) {
     size_t b = (m == n) ? plan_gemm(device, m, n, k, true).scratch : 0;
     s = a > b ? a : b;
     if (m == n && n >= 8 && n <= 256) { size_t f = fused_scratch_bytes(device, k, n); if (f > s) s = f; }
+    for (int sy = 0; sy < (m == n ? 2 : 1); sy++) {
+      const WsPlan wp = ws_plan(device, m, n, k, sy == 1, true);
+      if (wp.ok && wp.scratch > s) s = wp.scratch;
+    }
   }
   return s;
 }
@@ -775,8 +776,21 @@ int gemm_f64(int device, int64_t m, int64_t n, int64_t k, const double* a, int64
   if (sym && fused_applicable(k, n, a_cs, a) && scratch != nullptr && scratch_bytes >= fused_scratch_bytes(device, k, n))
     return glm_fused_stats(device, 0, a, k, n, a_cs, nullptr, NB_F64, nullptr, w, false, c, ldc, scratch,
                            scratch_bytes, st);
-  if (w == nullptr && !getenv("NUMS_B200_NO_WS") && gemm_ws_applicable(device, m, n, k, a, g.lda, b, g.ldb, c, ldc))
-    return gemm_ws_f64(m, n, k, a, g.lda, a_mc, b, g.ldb, b_nc, c, ldc, st);
+  if (!getenv("NUMS_B200_NO_WS") && gemm_ws_aligned(a, g.lda, b, g.ldb, w, c, ldc)) {
+    const WsPlan wp = ws_plan(device, m, n, k, sym, a_mc && b_nc);
+    if (wp.ok && (wp.scratch == 0 || (scratch != nullptr && scratch_bytes >= wp.scratch))) {
+      int rc = gemm_ws_f64(wp, m, n, k, a, g.lda, a_mc, b, g.ldb, b_nc, w, c, ldc, (double*)scratch, st);
+      if (rc || wp.scratch == 0) return rc;
+      g.tiles_m = wp.tiles_m; g.tiles_n = wp.tiles_n; g.ntiles = wp.ntiles; g.splits = wp.splits; g.sym = wp.sym;
+      g.kchunk = wp.kchunk;
+      g.part = (double*)scratch;
+      int64_t blocks = (m * n + 255) / 256;
+      if (blocks > 148 * 8) blocks = 148 * 8;
+      k_gemm_reduce<128, 128><<<(unsigned)blocks, 256, 0, st>>>(g);
+      NB_LAUNCH_CHECK();
+      return 0;
+    }
+  }
   GemmPlan p = plan_gemm(device, m, n, k, sym);
   g.tiles_m = p.tiles_m; g.tiles_n = p.tiles_n; g.ntiles = p.ntiles; g.splits = p.splits; g.sym = p.sym;
   g.kchunk = p.kchunk;

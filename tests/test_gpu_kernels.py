@@ -269,6 +269,34 @@ def test_tall_skinny_gram_and_vectors(K, n, d):
     assert rel_err(down(K.bop("tensordot", up(r), up(r), False, False, 1)), r @ r) < FTOL
 
 
+@pytest.mark.parametrize("n,d1,d2", [(60_000, 384, 384), (40_002, 512, 300), (30_000, 258, 1024), (9_000, 640, 640),
+                                     (2_000, 1024, 1024)])
+def test_tall_skinny_products_split_k_tma_path(K, n, d1, d2):
+    """A^T B of two tall blocks (few 128 x 128 output tiles, long contraction): the warp-specialised TMA kernel cut
+    along k, partial tiles summed in chunk order; the symmetric case computes the upper-triangular tiles only; the
+    weighted case X^T diag(w) X is what the Newton statistics use for d > 256."""
+    import ctypes as C
+    from nums_b200 import _lib, device as dv
+    rng = np.random.default_rng(n + d1)
+    A, B = rng.standard_normal((n, d1)), rng.standard_normal((n, d2))
+    Ad, Bd = up(A), up(B)
+    assert rel_err(down(K.bop("tensordot", Ad, Bd, True, False, 1)), A.T @ B) < FTOL
+    if d1 == d2:
+        G = down(K.bop("tensordot", Ad, Ad, True, False, 1))
+        assert rel_err(G, A.T @ A) < FTOL and np.array_equal(G, G.T)
+        w = rng.random(n) + 0.1
+        wd, out = up(w), dv.empty((d1, d1), np.float64, 0)
+        lib = _lib.load()
+        sc = dv.scratch(lib.nb_matmul_scratch_bytes(0, d1, d1, n), 0)
+        _lib.check(lib.nb_matmul_f64(0, d1, d1, n, Ad.ptr, 1, d1, Ad.ptr, d1, 1, wd.ptr, out.ptr, d1,
+                                     sc.data_ptr(), sc.numel(), dv.stream_ptr(0)))
+        H = down(out)
+        assert rel_err(H, (A * w[:, None]).T @ A) < FTOL and np.array_equal(H, H.T)
+    # B^T-layout operand (k contiguous on both sides): (d1 x n) @ (n x d2) with A^T materialised
+    At = up(np.ascontiguousarray(A.T))
+    assert rel_err(down(K.bop("tensordot", At, Bd, False, False, 1)), A.T @ B) < FTOL
+
+
 @pytest.mark.parametrize("p", [1, 2, 3, 17, 32, 33, 100, 257, 600])
 def test_inv_sizes(K, p):
     rng = np.random.default_rng(p)
