@@ -218,14 +218,22 @@ k_tri_gram(const FusedArgs a) {
   // ---------------------------------------------------------------- consumers
   const int bpc = W / a.KG;                        // blocks per CTA
   const int kg = warp / bpc;                       // which k4-steps of a stage this warp takes
-  const int t = c * bpc + (warp % bpc);
-  const bool has_block = t < a.T;
+  // Blocks are dealt to the C CTAs of a group from the list [diagonal blocks, then the others row by row], round robin,
+  // so that the diagonal blocks -- which skip their lower 8 x 8 tiles, 10 of 16 tile products -- are spread evenly.
+  const int u = (warp % bpc) * a.C + c;
+  const bool has_block = u < a.T;
   int bi = 0, bj = 0;
   if (has_block) {
-    int rem = t;
-    while (rem >= a.nblk - bi) { rem -= a.nblk - bi; bi++; }
-    bj = bi + rem;
+    if (u < a.nblk) {
+      bi = bj = u;
+    } else {
+      int rem = u - a.nblk;
+      while (rem >= a.nblk - 1 - bi) { rem -= a.nblk - 1 - bi; bi++; }
+      bj = bi + 1 + rem;
+    }
   }
+  const int t = bi * a.nblk - (bi * (bi - 1)) / 2 + (bj - bi);      // index in the row-by-row upper-triangular list
+  const bool diag = bi == bj;
   double acc[4][4][2];
 #pragma unroll
   for (int i = 0; i < 4; i++)
@@ -258,7 +266,8 @@ k_tri_gram(const FusedArgs a) {
 #pragma unroll
         for (int i = 0; i < 4; i++)
 #pragma unroll
-          for (int j = 0; j < 4; j++) f_dmma(acc[i][j][0], acc[i][j][1], af[cur][i], bf[cur][j]);
+          for (int j = 0; j < 4; j++)
+            if (j >= i || !diag) f_dmma(acc[i][j][0], acc[i][j][1], af[cur][i], bf[cur][j]);
       }
     } else if (has_block) {
       // few blocks (small d): KG warps share a block, each taking every KG-th group of four rows
@@ -275,7 +284,8 @@ k_tri_gram(const FusedArgs a) {
 #pragma unroll
         for (int i = 0; i < 4; i++)
 #pragma unroll
-          for (int j = 0; j < 4; j++) f_dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+          for (int j = 0; j < 4; j++)
+            if (j >= i || !diag) f_dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
       }
     }
     __syncwarp();

@@ -225,20 +225,20 @@ k_reduce_cols(const void* __restrict__ a, int adt, int64_t outer, int64_t len, i
     if (active && col < inner) {
       const int64_t base = o * len * inner + col;
       int64_t k = lo + tk;
-      T acc2 = R::identity(), acc3 = R::identity();
-      for (; k + 3 * (int64_t)kpar < hi; k += 4 * kpar) {
-        T v0 = load_as<T>(a, adt, base + k * inner);
-        T v1 = load_as<T>(a, adt, base + (k + kpar) * inner);
-        T v2 = load_as<T>(a, adt, base + (k + 2 * kpar) * inner);
-        T v3 = load_as<T>(a, adt, base + (k + 3 * kpar) * inner);
-        acc0 = R::combine(acc0, R::pre(v0));
-        acc1 = R::combine(acc1, R::pre(v1));
-        acc2 = R::combine(acc2, R::pre(v2));
-        acc3 = R::combine(acc3, R::pre(v3));
+      // eight rows in flight per thread: the walk is a pure stream, latency is hidden by the loads outstanding
+      T acc[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) acc[u] = R::identity();
+      for (; k + 7 * (int64_t)kpar < hi; k += 8 * kpar) {
+        T v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) v[u] = load_as<T>(a, adt, base + (k + (int64_t)u * kpar) * inner);
+#pragma unroll
+        for (int u = 0; u < 8; u++) acc[u] = R::combine(acc[u], R::pre(v[u]));
       }
-      for (; k < hi; k += kpar) acc0 = R::combine(acc0, R::pre(load_as<T>(a, adt, base + k * inner)));
-      acc0 = R::combine(acc0, acc2);
-      acc1 = R::combine(acc1, acc3);
+      for (; k < hi; k += kpar) acc[0] = R::combine(acc[0], R::pre(load_as<T>(a, adt, base + k * inner)));
+      acc0 = R::combine(R::combine(acc[0], acc[2]), R::combine(acc[4], acc[6]));
+      acc1 = R::combine(R::combine(acc[1], acc[3]), R::combine(acc[5], acc[7]));
     }
     __syncthreads();
     sm[t] = R::combine(acc0, acc1);
