@@ -164,6 +164,20 @@ int nb_pcg64_integers(int device, int64_t n, const uint64_t* state_hi_lo, const 
                       int64_t low, uint64_t rng, int64_t* out_d,
                       void* scratch_d, int64_t scratch_bytes, void* stream);
 
+/* ---- CSV ingest: the text of one read_csv_block call (nums/core/filesystem.py:227-283) parsed in HBM ------------
+ * The host uploads the lines of the block's byte range as raw text ending in '\n'.  nb_csv_count_rows counts
+ * them (one 8-byte read-back: the host sizes the output); nb_csv_parse trims "\r\n" from both ends of every
+ * line, splits it at `delimiter` into exactly `cols` fields and converts each like Python's float() (odt = NB_F64:
+ * correctly rounded, bit-identical to float(text); whitespace, sign, underscores, inf / nan) or int()
+ * (odt = NB_I64).  error_host = {failing line + 1 or 0, code, column}: 1 bad field, 2 wrong field count,
+ * 3 more than 19 significant digits with a rounding the device cannot decide, 4 hexadecimal float, 5 out of range.
+ * Both calls use the same scratch (nb_csv_scratch_bytes(nbytes, rows)) and synchronise `stream`. */
+int64_t nb_csv_scratch_bytes(int64_t nbytes, int64_t max_rows);
+int nb_csv_count_rows(int device, const unsigned char* text_d, int64_t nbytes, void* scratch_d, int64_t scratch_bytes,
+                      int64_t* rows_host, void* stream);
+int nb_csv_parse(int device, const unsigned char* text_d, int64_t nbytes, int64_t rows, int cols, int delimiter,
+                 int odt, void* out_d, void* scratch_d, int64_t scratch_bytes, int64_t* error_host, void* stream);
+
 /* ---- reductions: KernelCls.reduce_axis :294-313, sum_reduce :291, bop_reduce :433-453 -- */
 
 /* Views the input as [outer, len, inner] (C order) and reduces the middle axis:

@@ -101,9 +101,81 @@ class ArrayApplication:
     def eye(self, shape, block_shape, dtype=np.float64):
         return BlockArray.create("eye", shape, block_shape, dtype, self.km)
 
+    def _concatenate_general(self, arrays, axis, axis_block_size):
+        """application.py:271-335 for operands whose extents are not multiples of the block size (read_csv parts):
+        every destination block gathers the rectangles of the source blocks it overlaps (create_block)."""
+        import itertools
+        first = arrays[0]
+        nd = first.ndim
+        shape = list(first.shape)
+        shape[axis] = sum(a.shape[axis] for a in arrays)
+        block_shape = list(first.block_shape)
+        block_shape[axis] = axis_block_size
+        for ax in range(nd):
+            if ax != axis:
+                block_shape[ax] = first.shape[ax]      # off-axis: one block (re-blocked by the caller if needed)
+        grid = ArrayGrid(tuple(shape), tuple(block_shape), first.grid.dtype)
+        out = BlockArray(grid, self.km)
+        # source pieces along the axis: (array, block index along axis, global start, stop)
+        pieces, pos = [], 0
+        for a in arrays:
+            for g in range(a.grid.grid_shape[axis]):
+                lo = pos + g * a.block_shape[axis]
+                hi = min(pos + (g + 1) * a.block_shape[axis], pos + a.shape[axis])
+                pieces.append((a, g, lo, hi))
+            pos += a.shape[axis]
+        for entry in grid.get_entry_iterator():
+            d_lo = entry[axis] * block_shape[axis]
+            d_hi = min(d_lo + block_shape[axis], shape[axis])
+            oids, src_params, dst_params = [], [], []
+            for a, g, lo, hi in pieces:
+                s, e = max(lo, d_lo), min(hi, d_hi)
+                if s >= e:
+                    continue
+                # off-axis: the source may be blocked, the destination is not
+                off_ranges = []
+                for ax in range(nd):
+                    if ax == axis:
+                        off_ranges.append([g])
+                    else:
+                        off_ranges.append(list(range(a.grid.grid_shape[ax])))
+                for src_entry in itertools.product(*off_ranges):
+                    sb = a.blocks[src_entry]
+                    src_sel, dst_sel = [], []
+                    for ax in range(nd):
+                        if ax == axis:
+                            src_sel.append(slice(s - lo, e - lo))
+                            dst_sel.append(slice(s - d_lo, e - d_lo))
+                        else:
+                            o = src_entry[ax] * a.block_shape[ax]
+                            w = min(a.block_shape[ax], a.shape[ax] - o)
+                            src_sel.append(slice(0, w))
+                            dst_sel.append(slice(o, o + w))
+                    oids.append(sb.oid)
+                    src_params.append((tuple(src_sel), sb.transposed))
+                    dst_params.append((tuple(dst_sel), False))
+            db = out.blocks[entry]
+            db.oid = self.km.create_block(*oids, src_params=src_params, dst_params=dst_params, dst_shape=db.shape,
+                                          dst_shape_bc=None, syskwargs=db.syskwargs())
+        return out
+
     def concatenate(self, arrays, axis, axis_block_size=None):
-        """Block-aligned concatenation: blocks are referenced, not copied (the zero-copy case of
-        application.py:271-335 / view.py:256)."""
+        """application.py:271-335.  Block-aligned operands are referenced, not copied (the zero-copy case, view.py:256);
+        anything else is gathered block by block."""
+        try:
+            return self._concatenate_aligned(arrays, axis, axis_block_size)
+        except NotImplementedError:
+            first = arrays[0]
+            if any(a.ndim != first.ndim or a.dtype != first.dtype for a in arrays):
+                raise
+            for a in arrays:
+                for ax in range(first.ndim):
+                    if ax != axis and a.shape[ax] != first.shape[ax]:
+                        raise
+            bs = first.block_shape[axis] if axis_block_size is None else axis_block_size
+            return self._concatenate_general(arrays, axis, bs)
+
+    def _concatenate_aligned(self, arrays, axis, axis_block_size=None):
         first = arrays[0]
         nd = first.ndim
         for a in arrays:
@@ -164,6 +236,37 @@ class ArrayApplication:
             X = X.astype(np.float64)
         count = int(np.prod(X.shape)) if axis is None else X.shape[axis]
         return self.sum(X, axis=axis, keepdims=keepdims) / count
+
+    # ---- ingest (application.py:72-78, 172-190)
+    @property
+    def fs(self):
+        if getattr(self, "_fs", None) is None:
+            from .filesystem import FileSystem
+            self._fs = FileSystem(self.km)
+        return self._fs
+
+    def read_csv(self, filename, dtype=float, delimiter=",", has_header=False, num_workers=None):
+        if num_workers is None:
+            num_workers = self.km.num_cores_total()
+        arrays = self.fs.read_csv(filename, dtype, delimiter, has_header, num_workers)
+        shape = tuple(int(v) for v in np.sum([a.shape for a in arrays], axis=0))
+        shape = (shape[0],) + tuple(arrays[0].shape[1:])
+        out_dtype = np.int64 if dtype is int else dtype
+        block_shape = self.km.get_block_shape(shape, out_dtype)
+        result = self.concatenate(arrays, axis=0, axis_block_size=block_shape[0])
+        del arrays
+        if len(block_shape) > 1 and result.block_shape[1] != block_shape[1]:
+            result = result.reshape(block_shape=block_shape)
+        return result
+
+    def write_fs(self, ba, filename):
+        return self.fs.write_fs(ba, filename)
+
+    def read_fs(self, filename):
+        return self.fs.read_fs(filename)
+
+    def delete_fs(self, filename):
+        return self.fs.delete_fs(filename)
 
     def cov(self, X, rowvar=True, bias=False, dtype=None):
         # application.py:531-540

@@ -106,6 +106,17 @@ def scratch(nbytes, device_index):
 _PIN_CHUNK = 1 << 28   # 256 MiB staging chunks for large uploads
 
 
+def upload_bytes(data, device_index):
+    """Raw bytes -> uint8 tensor in HBM (256-byte aligned): the text buffer of the CSV ingest path."""
+    require_cuda()
+    src = torch.frombuffer(bytearray(data), dtype=torch.uint8)
+    out = torch.empty(max(len(data), 8), dtype=torch.uint8, device=torch.device("cuda", device_index))
+    for lo in range(0, len(data), _PIN_CHUNK):
+        hi = min(len(data), lo + _PIN_CHUNK)
+        out[lo:hi].copy_(src[lo:hi], non_blocking=False)
+    return out
+
+
 def from_numpy(arr, device_index):
     """Host ndarray / NumPy scalar -> DeviceBlock (H2D copy through pinned staging)."""
     require_cuda()

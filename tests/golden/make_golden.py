@@ -332,6 +332,51 @@ def main():
     outL["inv_uppertri"] = linalg.inv_uppertri(app, app.array(Rup, block_shape=(3, 3))).get()
     save("linalg", **outL)
 
+    # ---------------------------------------------------------------- CSV ingest (filesystem.py:227-283, 615-657)
+    from nums.core import filesystem as ref_fs
+    from nums.core.storage import utils as storage_utils
+    rngc = np.random.default_rng(77)
+    vals = rngc.standard_normal((257, 5)) * 10.0 ** rngc.integers(-30, 30, size=(257, 5))
+    rows = []
+    for i, r in enumerate(vals):
+        fmt = ["%.18e", "%r", "%.6f", "%g", "%.17g"][i % 5]
+        rows.append(",".join((fmt % v) if fmt != "%r" else repr(float(v)) for v in r))
+    rows[3] = " 1.5 ,\t-2e3,+.5,7.,1_000.25"                      # whitespace, signs, bare dots, underscores
+    rows[4] = "inf,-Infinity,nan,0.0,-0.0"
+    rows[5] = "4.9e-324,2.2250738585072011e-308,1.7976931348623157e308,1e309,1e-400"
+    rows[6] = "9007199254740993,9007199254740992.5,0.1000000000000000055511151231257827,123456789012345678901234567890,5e-1"
+    csv_text = "c0,c1,c2,c3,c4\n" + "\n".join(rows) + "\n"
+    csv_path = os.path.join(tmp, "golden.csv")
+    with open(csv_path, "w", encoding="utf-8") as fh:
+        fh.write(csv_text)
+    size = storage_utils.get_file_size(csv_path)
+    outC = {"csv_bytes": np.frombuffer(csv_text.encode(), dtype=np.uint8).copy()}
+    for nw in (1, 4, 7):
+        bts = storage_utils.Batch.from_num_batches(size, nw).batches
+        outC["batches_%d" % nw] = np.array(bts, dtype=i64)
+        for bi, (s0, e0) in enumerate(bts):
+            arr, shp = ref_fs.read_csv_block(csv_path, s0, e0, float, ",", True)
+            outC["w%d_b%d" % (nw, bi)] = arr
+    # integer file, no header, dtype np.int64 and python int
+    int_rows = [",".join(str(int(v)) for v in rngc.integers(-10 ** 15, 10 ** 15, size=3)) for _ in range(40)]
+    int_text = "\n".join(int_rows) + "\n"
+    int_path = os.path.join(tmp, "golden_int.csv")
+    with open(int_path, "w", encoding="utf-8") as fh:
+        fh.write(int_text)
+    outC["int_bytes"] = np.frombuffer(int_text.encode(), dtype=np.uint8).copy()
+    arr, _ = ref_fs.read_csv_block(int_path, 0, len(int_text), np.int64, ",", False)
+    outC["int64_all"] = arr
+    dec_rows = ["%.3f,%.1f,%d" % (a, b, c) for a, b, c in zip(rngc.standard_normal(30) * 100, rngc.standard_normal(30) * 1e6,
+                                                               rngc.integers(-99, 99, size=30))]
+    dec_text = "\n".join(dec_rows) + "\n"
+    dec_path = os.path.join(tmp, "golden_dec.csv")
+    with open(dec_path, "w", encoding="utf-8") as fh:
+        fh.write(dec_text)
+    outC["dec_bytes"] = np.frombuffer(dec_text.encode(), dtype=np.uint8).copy()
+    arr, _ = ref_fs.read_csv_block(dec_path, 0, len(dec_text), int, ",", False)     # converter: int(float(x))
+    outC["pyint_all"] = arr
+    save("csv", **outC)
+
     # ---------------------------------------------------------------- block-shape rule
     cases = [((10 ** 8,), "float64", (8, 1), 8), ((10 ** 8, 256), "float64", (8, 1), 8),
              ((10 ** 8, 256), "float64", (2, 1), 2), ((10 ** 4, 10 ** 4), "float64", (4, 1), 4),

@@ -157,3 +157,24 @@ def test_linalg_oracle_matches_reference_outputs():
     assert rel_err(ol.indirect_tsr(XT, 512, 32), g["tall_tsr_R"]) <= tol
     assert rel_err(ol.inv_uppertri(g["uppertri"], 3), g["inv_uppertri"]) <= tol
     assert rel_err(np.linalg.cholesky(g["spd"]), g["chol_L"]) <= tol
+
+
+# ---------------------------------------------------------------- CSV ingest (nums/core/filesystem.py:227-283)
+def test_csv_oracle_matches_reference_blocks():
+    """oracle/csvio.py against the reference's own read_csv_block on every byte range of 1, 4 and 7 workers
+    (tests/golden/csv.npz): same lines per block, same float()/int() results, bit for bit."""
+    from oracle import csvio
+    g = load_golden("csv")
+    data = g["csv_bytes"].tobytes()
+    for nw in (1, 4, 7):
+        b = csvio.batches(len(data), nw)
+        assert np.array_equal(np.array(b), g["batches_%d" % nw])
+        for bi, (s, e) in enumerate(b):
+            got = csvio.read_csv_block(data, s, e, float, ",", True)
+            want = g["w%d_b%d" % (nw, bi)]
+            assert got.shape == want.shape
+            if want.size:
+                assert np.array_equal(got.view(np.uint64), want.view(np.uint64))
+        assert csvio.read_csv(data, float, ",", True, nw).shape == (257, 5)
+    assert np.array_equal(csvio.read_csv_block(g["int_bytes"].tobytes(), 0, len(g["int_bytes"]), np.int64), g["int64_all"])
+    assert np.array_equal(csvio.read_csv_block(g["dec_bytes"].tobytes(), 0, len(g["dec_bytes"]), int), g["pyint_all"])
