@@ -164,6 +164,14 @@ int nb_pcg64_integers(int device, int64_t n, const uint64_t* state_hi_lo, const 
                       int64_t low, uint64_t rng, int64_t* out_d,
                       void* scratch_d, int64_t scratch_bytes, void* stream);
 
+/* KernelCls.permutation (numpy_kernel.py:112-114): out = Generator(PCG64(seed).jumped(j)).permutation(n), bit-identical,
+ * n < 2^31.  NumPy's Fisher-Yates with masked-rejection draws is restated as parallel passes (csrc/perm.cu): the
+ * sample each draw uses is found phase by phase with bracketed prefix sums, the composition of the n - 1 swaps by
+ * per-target step lists and pointer jumping.  Synchronises `stream` several times per phase (convergence tests). */
+int64_t nb_pcg64_permutation_scratch_bytes(int64_t n);
+int nb_pcg64_permutation(int device, int64_t n, const uint64_t* state_hi_lo, const uint64_t* inc_hi_lo,
+                         int64_t* out_d, void* scratch_d, int64_t scratch_bytes, void* stream);
+
 /* ---- CSV ingest: the text of one read_csv_block call (nums/core/filesystem.py:227-283) parsed in HBM ------------
  * The host uploads the lines of the block's byte range as raw text ending in '\n'.  nb_csv_count_rows counts
  * them (one 8-byte read-back: the host sizes the output); nb_csv_parse trims "\r\n" from both ends of every

@@ -34,6 +34,9 @@ SIGNATURES = {
     "nb_eye": (c_int, [c_int, c_i64, c_i64, c_vp, c_int, c_vp]),
     "nb_copy_strided": (c_int, [c_int, c_int, P_I64, c_int, c_vp, P_I64, c_vp, P_I64, c_vp]),
     "nb_pcg64_random": (c_int, [c_int, c_i64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), c_vp, c_vp]),
+    "nb_pcg64_permutation_scratch_bytes": (c_i64, [c_i64]),
+    "nb_pcg64_permutation": (c_int, [c_int, c_i64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), c_vp, c_vp, c_i64,
+                                     c_vp]),
     "nb_csv_scratch_bytes": (c_i64, [c_i64, c_i64]),
     "nb_csv_count_rows": (c_int, [c_int, c_vp, c_i64, c_vp, c_i64, C.POINTER(C.c_int64), c_vp]),
     "nb_csv_parse": (c_int, [c_int, c_vp, c_i64, c_i64, c_int, c_int, c_int, c_vp, c_vp, c_i64, C.POINTER(C.c_int64),

@@ -176,8 +176,20 @@ class KernelCls:
         return DeviceBlock(out.t.view(tuple(shape)))
 
     def permutation(self, rng_params, size, device_index=None):
-        # numpy_kernel.py:112-114
-        return dv.from_numpy(block_rng(*rng_params).permutation(size), _cur(device_index))
+        # numpy_kernel.py:112-114, generated in HBM (csrc/perm.cu), bit-identical to the host generator's shuffle
+        dev = _cur(device_index)
+        size = int(size)
+        if size >= 2 ** 31:
+            return dv.from_numpy(block_rng(*rng_params).permutation(size), dev)
+        lib = _lib.load()
+        state, inc = self._stream_state(rng_params)
+        out = dv.empty((size,), np.int64, dev)
+        if size == 0:
+            return out
+        sc = dv.scratch(lib.nb_pcg64_permutation_scratch_bytes(size), dev)
+        _lib.check(lib.nb_pcg64_permutation(dev, size, state, inc, out.ptr, sc.data_ptr(), sc.numel(),
+                                            dv.stream_ptr(dev)))
+        return out
 
     def create_block(self, *src_arrs, src_params, dst_params, dst_shape, dst_shape_bc):
         # numpy_kernel.py:116-129: gather sub-rectangles of several blocks into a new block

@@ -390,6 +390,17 @@ def test_device_block_rng_integers_is_bit_identical(K, low, high, endpoint):
         np.testing.assert_array_equal(got, want)
 
 
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 17, 1000, 4097, 100_003, 2 ** 20 - 1, 2 ** 20, 2 ** 20 + 1, 3_000_000])
+def test_device_block_rng_permutation_is_bit_identical(K, n):
+    """KernelCls.permutation: NumPy's Fisher-Yates (masked-rejection draws on 32-bit half-words, swaps from the top)
+    restated as prefix sums and pointer jumping (csrc/perm.cu); one wrong acceptance would change every later draw."""
+    for jump in (0, 7):
+        got = down(K.permutation((1337, jump), n, device_index=0))
+        want = ok.block_rng(1337, jump).permutation(n)
+        assert got.dtype == np.int64
+        np.testing.assert_array_equal(got, want)
+
+
 def test_device_block_rng_integers_rejects_bad_bounds(K):
     with pytest.raises(ValueError):
         K.random_block((1, 0), "integers", (5, 5, 10, np.int64, False), (10,), np.int64, device_index=0)
