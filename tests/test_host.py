@@ -199,3 +199,14 @@ def test_rng_stream_matches_reference_rule():
     a = cuda_kernel.block_rng(*p1).normal(0.0, 1.0, 5)
     b = ok.random_block(p1, "normal", (0.0, 1.0, 5), (5,), np.float64)
     np.testing.assert_array_equal(a, b)
+
+
+def test_parallel_permutation_formulation_equals_numpy():
+    """The prefix-sum / pointer-jumping restatement of NumPy's Fisher-Yates that csrc/perm.cu implements, run in NumPy
+    (tools/perm_prototype.py): identical to Generator.permutation for sizes around the mask boundaries."""
+    from numpy.random import PCG64, Generator
+    from tools import perm_prototype as pp
+    for n in (1, 2, 3, 4, 5, 8, 9, 255, 256, 257, 1000, 65537, 200_003):
+        for jump in (0, 5):
+            got, _, rounds, _ = pp.permutation(n, 99, jump)
+            assert np.array_equal(got, Generator(PCG64(99).jumped(jump)).permutation(n)), (n, jump)

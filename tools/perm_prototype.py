@@ -1,3 +1,7 @@
+"""NumPy prototype of the parallel formulation of Generator.permutation that csrc/perm.cu implements: (A) the sample
+each Fisher-Yates draw uses, found per mask phase with bracketed prefix sums; (B) the composition of the swaps through
+per-target step lists and pointer jumping.  `python tools/perm_prototype.py [n]` checks it against NumPy;
+tests/test_host.py runs it on the CPU so the algorithm itself is covered without a GPU."""
 import numpy as np, sys, time
 from numpy.random import PCG64, Generator
 
@@ -72,10 +76,20 @@ def apply_swaps(n, J):
     a[0] = W[parent[0]] if parent[0] >= 0 else 0
     return a, rounds
 
-for n in [2, 3, 5, 17, 1000, 4097, 100003, int(sys.argv[1]) if len(sys.argv) > 1 else 1000000]:
-    h = halves_of(1337, 3, 3 * n + 4096)
-    t0 = time.time()
+def permutation(n, seed, jump):
+    """Generator(PCG64(seed).jumped(jump)).permutation(n) through the parallel formulation; also returns the number
+    of samples consumed, bracket rounds (all phases) and pointer-jumping rounds."""
+    if n < 2:
+        return np.arange(n, dtype=np.int64), 0, 0, 0
+    h = halves_of(seed, jump, 3 * n + 4096)
     J, used, its = resolve_draws(n, h)
     a, rounds = apply_swaps(n, J)
-    b = Generator(PCG64(1337).jumped(3)).permutation(n)
-    print(n, np.array_equal(a, b), "samples", used, "iters", its, "jump rounds", rounds, "%.2fs" % (time.time() - t0))
+    return a, used, its, rounds
+
+
+if __name__ == "__main__":
+    for n in [2, 3, 5, 17, 1000, 4097, 100003, int(sys.argv[1]) if len(sys.argv) > 1 else 1000000]:
+        t0 = time.time()
+        a, used, its, rounds = permutation(n, 1337, 3)
+        b = Generator(PCG64(1337).jumped(3)).permutation(n)
+        print(n, np.array_equal(a, b), "samples", used, "iters", its, "jump rounds", rounds, "%.2fs" % (time.time() - t0))
