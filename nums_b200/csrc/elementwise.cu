@@ -3,6 +3,7 @@
 // 316-347, 414-431.  All of these are HBM-bound streaming kernels: grid-stride loops sized in
 // multiples of the SM count, 4 independent 8-byte loads in flight per thread and operand.
 #include "common.cuh"
+#include <type_traits>
 
 namespace nb {
 
@@ -252,8 +253,51 @@ k_bop_strided(int64_t n, Strides4 s, const void* __restrict__ a, int adt,
 template <int OP, typename C>
 __global__ void __launch_bounds__(EW_THREADS)
 k_bop_2d(int64_t rows, int64_t cols, const void* __restrict__ a, int adt, int64_t ars, int64_t acs,
-         const void* __restrict__ b, int bdt, int64_t brs, int64_t bcs, void* __restrict__ out, int odt) {
+         const void* __restrict__ b, int bdt, int64_t brs, int64_t bcs, void* __restrict__ out, int odt, int vec) {
   using R = typename BopResult<OP, C>::type;
+  // float64 (op) float64 -> float64 with an even column count and 16-byte aligned rows: two adjacent columns per
+  // thread (16-byte loads / stores on the contiguous operands, one division per pair), four pairs in flight.
+  // This is the s * X product of glms.py:495-496 in the unfused path.
+  if constexpr (std::is_same<C, double>::value && std::is_same<R, double>::value) {
+    if (vec) {
+      const int64_t hc = cols >> 1, pairs = rows * hc;
+      const double* pa = (const double*)a;
+      const double* pb = (const double*)b;
+      double* po = (double*)out;
+      const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
+      const bool small = hc < (1u << 31) && pairs < (1ll << 31);
+      const unsigned uhc = (unsigned)(small ? hc : 1);
+      for (int64_t l0 = (int64_t)blockIdx.x * EW_THREADS + threadIdx.x; l0 < pairs; l0 += stride * 4) {
+        double2 av[4], bv[4];
+        int64_t off[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int64_t l = l0 + (int64_t)u * stride;
+          off[u] = -1;
+          if (l < pairs) {
+            int64_t r, c2;
+            if (small) { const unsigned q = (unsigned)l / uhc; r = q; c2 = (unsigned)l - q * uhc; }
+            else { r = l / hc; c2 = l - r * hc; }
+            off[u] = 2 * l;
+            if (acs == 0) { const double t = pa[r * ars]; av[u] = make_double2(t, t); }
+            else av[u] = *reinterpret_cast<const double2*>(pa + r * ars + 2 * c2);
+            if (bcs == 0) { const double t = pb[r * brs]; bv[u] = make_double2(t, t); }
+            else bv[u] = *reinterpret_cast<const double2*>(pb + r * brs + 2 * c2);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          if (off[u] >= 0) {
+            double2 o;
+            o.x = bop_apply<OP>(av[u].x, bv[u].x);
+            o.y = bop_apply<OP>(av[u].y, bv[u].y);
+            *reinterpret_cast<double2*>(po + off[u]) = o;
+          }
+        }
+      }
+      return;
+    }
+  }
   // Each CTA walks bands of whole rows; inside a band the (row, col) split is a 32-bit division and four
   // independent element loads are in flight per thread.
   const int64_t band = cols >= (1 << 20) ? 1 : ((int64_t)EW_THREADS * EW_UNROLL * 4 + cols - 1) / cols;   // rows per band
@@ -322,8 +366,16 @@ static int launch_bop(int device, int ndim, const int64_t* shape, const void* a,
   }
   int grid = grid_for(device, n, EW_THREADS, s.shape[0] == 1 && s.shape[1] == 1 ? EW_UNROLL * 4 : 1);
   if (s.shape[0] == 1 && s.shape[1] == 1) {
+    // vector path: all float64, even column count, every operand either column-broadcast or contiguous along the
+    // columns with 16-byte aligned rows
+    auto side_ok = [&](const void* p, int64_t rs, int64_t cs) {
+      if (cs == 0) return true;
+      return cs == 1 && (rs & 1) == 0 && (((uintptr_t)p) & 15) == 0;
+    };
+    const int vec = (adt == NB_F64 && bdt == NB_F64 && odt == NB_F64 && (s.shape[3] & 1) == 0 &&
+                     (((uintptr_t)out) & 15) == 0 && side_ok(a, s.sa[2], s.sa[3]) && side_ok(b, s.sb[2], s.sb[3])) ? 1 : 0;
     k_bop_2d<OP, C><<<grid, EW_THREADS, 0, st>>>(s.shape[2], s.shape[3], a, adt, s.sa[2], s.sa[3], b, bdt,
-                                                s.sb[2], s.sb[3], out, odt);
+                                                s.sb[2], s.sb[3], out, odt, vec);
   } else {
     k_bop_strided<OP, C><<<grid, EW_THREADS, 0, st>>>(n, s, a, adt, b, bdt, out, odt);
   }

@@ -32,3 +32,10 @@ for d in (64, 256, 1024):
     show("X@b   (%d x %d)" % (rows, d), timeit(lambda: K.bop("tensordot", X, b, False, False, 1)), 8 * rows * d)
     show("X^T@r (%d x %d)" % (rows, d), timeit(lambda: K.bop("tensordot", X, r, True, False, 1)), 8 * rows * d)
     show("sum axis=0 (%d x %d)" % (rows, d), timeit(lambda: K.reduce_axis("sum", X, 0, False, False)), 8 * rows * d)
+for d in (64, 256):
+    rows = n // d
+    X = dv.DeviceBlock(x.t[: rows * d].view(rows, d))
+    col = dv.DeviceBlock(x.t[:rows].view(rows, 1))
+    rowv = dv.DeviceBlock(x.t[:d].view(1, d))
+    show("(n,1)*(n,%d) broadcast mul" % d, timeit(lambda: K.bop("mul", col, X, False, False, {})), 16 * rows * d + 8 * rows)
+    show("(n,%d)-(1,%d) broadcast sub" % (d, d), timeit(lambda: K.bop("sub", X, rowv, False, False, {})), 16 * rows * d)
