@@ -202,12 +202,50 @@ constexpr int EW_UNROLL = 4;
 template <int OP, typename C>
 __global__ void __launch_bounds__(EW_THREADS)
 k_bop_flat(int64_t n, const void* __restrict__ a, int adt, int a_scalar,
-           const void* __restrict__ b, int bdt, int b_scalar, void* __restrict__ out, int odt) {
+           const void* __restrict__ b, int bdt, int b_scalar, void* __restrict__ out, int odt, int pack) {
   using R = typename BopResult<OP, C>::type;
   const int64_t stride = (int64_t)gridDim.x * EW_THREADS * EW_UNROLL;
   C as = C(), bs = C();
   if (a_scalar) as = load_as<C>(a, adt, 0);
   if (b_scalar) bs = load_as<C>(b, bdt, 0);
+  // Comparisons of 8-byte operands (x == c on 10^8 int64): a warp takes 256 consecutive elements with coalesced
+  // 8-byte loads, turns the eight result ballots into bytes and every lane stores 8 bools at once (one-byte stores
+  // held this at 74 % of the HBM rate).
+  if constexpr (std::is_same<R, bool>::value && sizeof(C) == 8) {
+    if (pack) {
+      const C* pa = (const C*)a;
+      const C* pb = (const C*)b;
+      const int lane = threadIdx.x & 31;
+      const int64_t warps = (int64_t)gridDim.x * (EW_THREADS / 32);
+      const int64_t full_groups = n / 256;
+      for (int64_t gi = (int64_t)blockIdx.x * (EW_THREADS / 32) + (threadIdx.x >> 5); gi < full_groups; gi += warps) {
+        const int64_t e0 = gi * 256;
+        C av[8], bv[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+          av[u] = a_scalar ? as : pa[e0 + 32 * u + lane];
+          bv[u] = b_scalar ? bs : pb[e0 + 32 * u + lane];
+        }
+        unsigned mine = 0;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+          const unsigned m = __ballot_sync(0xffffffffu, bop_apply<OP>(av[u], bv[u]));
+          if ((lane >> 2) == u) mine = m;
+        }
+        const unsigned bits = (mine >> (8 * (lane & 3))) & 0xffu;       // results of elements 8 lane .. 8 lane + 7
+        unsigned long long packed = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) packed |= (unsigned long long)((bits >> k) & 1u) << (8 * k);
+        *reinterpret_cast<unsigned long long*>((unsigned char*)out + e0 + 8 * lane) = packed;
+      }
+      // tail (< 256 elements) by the first CTA
+      if (blockIdx.x == 0) {
+        for (int64_t i = full_groups * 256 + threadIdx.x; i < n; i += EW_THREADS)
+          store_as<R>(out, odt, i, bop_apply<OP>(a_scalar ? as : pa[i], b_scalar ? bs : pb[i]));
+      }
+      return;
+    }
+  }
   for (int64_t base = (int64_t)blockIdx.x * EW_THREADS * EW_UNROLL + threadIdx.x; base < n; base += stride) {
     C av[EW_UNROLL], bv[EW_UNROLL];
 #pragma unroll
@@ -352,8 +390,11 @@ static int launch_bop(int device, int ndim, const int64_t* shape, const void* a,
   }
   if ((a_contig || a_scalar) && (b_contig || b_scalar)) {
     int grid = grid_for(device, n, EW_THREADS, EW_UNROLL);
+    const int ccode = std::is_same<C, double>::value ? NB_F64 : (std::is_same<C, int64_t>::value ? NB_I64 : NB_BOOL);
+    const int pack = (odt == NB_BOOL && adt == ccode && bdt == ccode && sizeof(C) == 8 && n >= 4096 &&
+                      (((uintptr_t)out) & 7) == 0) ? 1 : 0;
     k_bop_flat<OP, C><<<grid, EW_THREADS, 0, st>>>(n, a, adt, a_scalar && !a_contig ? 1 : 0, b, bdt,
-                                                  b_scalar && !b_contig ? 1 : 0, out, odt);
+                                                  b_scalar && !b_contig ? 1 : 0, out, odt, pack);
     NB_LAUNCH_CHECK();
     return 0;
   }

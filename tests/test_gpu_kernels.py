@@ -193,6 +193,12 @@ def test_elementwise_sizes(K, n):
     np.testing.assert_array_equal(down(K.bop("floor_divide", up(ia), up(ib), False, False, {})),
                                   ok.bop("floor_divide", ia, ib))
     np.testing.assert_array_equal(down(K.bop("eq", up(ib), up(np.int64(7)), False, False, {})), ib == 7)
+    # comparisons of 8-byte operands pack eight results per store above 4096 elements; NaN compares false
+    a[::17] = np.nan
+    for op, fn in (("lt", np.less), ("ge", np.greater_equal), ("ne", np.not_equal)):
+        np.testing.assert_array_equal(down(K.bop(op, up(a), up(b), False, False, {})), fn(a, b))
+        np.testing.assert_array_equal(down(K.bop(op, up(np.float64(0.25)), up(b), False, False, {})), fn(0.25, b))
+    np.testing.assert_array_equal(down(K.bop("le", up(ia), up(ib), False, False, {})), ia <= ib)
 
 
 @pytest.mark.parametrize("shape,axis", [((1,), None), ((5000,), None), ((3_000_017,), None), ((2000, 3), 0),

@@ -39,3 +39,8 @@ for d in (64, 256):
     rowv = dv.DeviceBlock(x.t[:d].view(1, d))
     show("(n,1)*(n,%d) broadcast mul" % d, timeit(lambda: K.bop("mul", col, X, False, False, {})), 16 * rows * d + 8 * rows)
     show("(n,%d)-(1,%d) broadcast sub" % (d, d), timeit(lambda: K.bop("sub", X, rowv, False, False, {})), 16 * rows * d)
+xi = K.astype(dv.DeviceBlock(x.t[:n]), "int64")
+ci = dv.from_numpy(np.int64(3), 0)
+show("x == c  (int64 -> bool, 1e8)", timeit(lambda: K.bop("eq", xi, ci, False, False, {})), 9 * n)
+show("x < y   (f64, f64 -> bool, 1e8)", timeit(lambda: K.bop("lt", x, x, False, False, {})), 17 * n)
+show("argmax int64 1e8", timeit(lambda: K.arg_op("argmax", xi, slice(0, n))), 8 * n)
