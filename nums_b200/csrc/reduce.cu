@@ -441,14 +441,20 @@ k_argop_stage1(int64_t n, const T* __restrict__ a, int64_t chunk, T* __restrict_
   T best = T(0);
   int64_t bi = -1;
   int64_t i = lo + threadIdx.x;
-  for (; i + 3 * RED_THREADS < hi; i += 4 * RED_THREADS) {
-    T v[4];
+  // eight loads in flight, two independent (value, index) chains merged with the same ordering rule
+  T best2 = T(0);
+  int64_t bi2 = -1;
+  for (; i + 7 * RED_THREADS < hi; i += 8 * RED_THREADS) {
+    T v[8];
 #pragma unroll
-    for (int u = 0; u < 4; u++) v[u] = a[i + u * RED_THREADS];
+    for (int u = 0; u < 8; u++) v[u] = a[i + u * RED_THREADS];
 #pragma unroll
-    for (int u = 0; u < 4; u++)
+    for (int u = 0; u < 8; u += 2) {
       if (arg_better<IS_MAX, T>(v[u], i + u * RED_THREADS, best, bi)) { best = v[u]; bi = i + u * RED_THREADS; }
+      if (arg_better<IS_MAX, T>(v[u + 1], i + (u + 1) * RED_THREADS, best2, bi2)) { best2 = v[u + 1]; bi2 = i + (u + 1) * RED_THREADS; }
+    }
   }
+  if (arg_better<IS_MAX, T>(best2, bi2, best, bi)) { best = best2; bi = bi2; }
   for (; i < hi; i += RED_THREADS) {
     T v = a[i];
     if (arg_better<IS_MAX, T>(v, i, best, bi)) { best = v; bi = i; }
