@@ -366,6 +366,9 @@ size_t glm_regs_scratch_bytes(int device, int64_t d, int want_hess);
 int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                    const double* beta, int want_hess, double* stats, void* scratch, size_t scratch_bytes,
                    cudaStream_t st);
+bool glm_regs_pass1_applicable(int64_t d);
+int glm_regs_pass1(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                   const double* beta, double* wbuf, double* stats, void* scratch, size_t scratch_bytes, cudaStream_t st);
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
 int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
@@ -408,7 +411,12 @@ static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
   if (want_hess && d >= 8) cur += align256((size_t)n * sizeof(double));
   L.off_parts = cur;
   size_t per = d >= 8 ? (size_t)(2 * d + 3) : 64;
-  cur += align256((size_t)L.max_parts * per * sizeof(double));
+  size_t parts_bytes = (size_t)L.max_parts * per * sizeof(double);
+  if (want_hess && glm_regs_pass1_applicable(d)) {
+    const size_t r = glm_regs_scratch_bytes(device, d, 0);
+    if (r > parts_bytes) parts_bytes = r;
+  }
+  cur += align256(parts_bytes);
   L.off_gemm = cur;
   if (want_hess && d >= 8) cur += align256(gemm_scratch_bytes(device, d, d, n));
   if (want_hess && d >= 8 && d <= 256) {   // the triangular / single-pass kernels take their partials from the GEMM region
@@ -541,6 +549,14 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   int nparts = 0;
   const bool vec = ((ldx & 1) == 0) && ((((uintptr_t)x_d) & 15) == 0);
   int rc;
+  if (tri_ok && glm_mode() == 0 && glm_regs_pass1_applicable(d)) {
+    // 64 < d <= 192: the register-resident kernel is the faster first pass (its partials live in the parts region)
+    rc = glm_regs_pass1(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, stats_d, parts,
+                        L.off_gemm - L.off_parts, st);
+    if (rc) return rc;
+    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, false, stats_d, d + 1,
+                           sc + L.off_gemm, L.total - L.off_gemm, st);
+  }
   if (rows_mode() == 1 && rows_tma_applicable(n, d, ldx, x_d))
     rc = glm_rows_tma(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, a.wbuf, parts, L.max_parts, &nparts, st);
   else

@@ -32,27 +32,34 @@ struct RegsArgs {
   const void* y; int ydt;
   const double* beta;
   int family;
+  double* wbuf;       // mode 2: the Hessian weights w (n doubles) for the second pass, or null
   double* parts;      // per CTA: [dd*dd tiles | g dd | u dd | sum r | sum w | obj]
 };
 
 // per-CTA partial (and shared-memory reduction buffer): [DD*DD tiles (Hessian variant only) | g DD | u DD | 3 sums]
-template <int NB, bool HESS> struct RegsLayout {
+// MODE 0: gradient + objective; 1: Newton statistics with the tile products; 2: first pass of the two-pass Newton
+// (g, the intercept column u, sum w, objective, and the weights written out for glm_fused.cu)
+template <int NB, int MODE> struct RegsLayout {
   static constexpr int DD = 8 * NB;
-  static constexpr int G_OFF = HESS ? DD * DD : 0, U_OFF = G_OFF + DD, S_OFF = U_OFF + DD, LEN = S_OFF + 3;
+  static constexpr int G_OFF = MODE == 1 ? DD * DD : 0, U_OFF = G_OFF + DD, S_OFF = U_OFF + DD, LEN = S_OFF + 3;
 };
 
 // rows per batch = 4 * BATCH: the link function of a batch is evaluated once, lane (q, g) taking row 4 (g % BATCH) + q,
 // and handed to the lanes that need it by shuffles; BATCH is bounded by the registers the x values of a batch take
-template <int NB, bool HESS> struct RegsBatch {
-  static constexpr int value = !HESS ? (NB <= 8 ? 8 : (NB <= 16 ? 4 : 2)) : (NB <= 4 ? 8 : (NB <= 6 ? 4 : 2));
+template <int NB, int MODE> struct RegsBatch {
+  static constexpr int value = MODE == 0 ? (NB <= 8 ? 8 : (NB <= 16 ? 4 : 2))
+                             : MODE == 1 ? (NB <= 4 ? 8 : (NB <= 6 ? 4 : 2))
+                                         : (NB <= 8 ? 8 : (NB <= 12 ? 4 : 2));
 };
 
-template <int NB, bool HESS>
+template <int NB, int MODE>
 __global__ void __launch_bounds__(RG_THREADS)
 k_glm_regs(RegsArgs a) {
-  using L = RegsLayout<NB, HESS>;
+  using L = RegsLayout<NB, MODE>;
   constexpr int DD = L::DD;
-  constexpr int BATCH = RegsBatch<NB, HESS>::value;
+  constexpr int BATCH = RegsBatch<NB, MODE>::value;
+  constexpr bool HESS = MODE == 1;                // tile products
+  constexpr bool WANT_U = MODE >= 1;              // intercept column and sum of weights
   constexpr bool BET_SMEM = NB > 16;              // wide gradient-only variants keep beta in shared memory
   extern __shared__ double red[];                 // L::LEN doubles (+ DD of beta)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -71,11 +78,11 @@ k_glm_regs(RegsArgs a) {
   double acc[HESS ? NB * (NB + 1) / 2 : 1][2];
 #pragma unroll
   for (int t = 0; t < (HESS ? NB * (NB + 1) / 2 : 1); ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
-  double gacc[NB], uacc[HESS ? NB : 1];
+  double gacc[NB], uacc[WANT_U ? NB : 1];
 #pragma unroll
   for (int I = 0; I < NB; ++I) gacc[I] = 0.0;
 #pragma unroll
-  for (int I = 0; I < (HESS ? NB : 1); ++I) uacc[I] = 0.0;
+  for (int I = 0; I < (WANT_U ? NB : 1); ++I) uacc[I] = 0.0;
   double sr = 0.0, sw = 0.0, sobj = 0.0;
 
   constexpr int ROWS = 4 * BATCH;
@@ -109,22 +116,25 @@ k_glm_regs(RegsArgs a) {
     LinkOut lo = glm_link_rt(a.family, my_eta + b0, yv);
     if (!live) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
     sr += lo.resid; sobj += lo.obj;
-    if constexpr (HESS) sw += lo.wgt;
+    if constexpr (WANT_U) sw += lo.wgt;
+    if constexpr (MODE == 2) { if (live && a.wbuf) a.wbuf[rl] = lo.wgt; }
 #pragma unroll
     for (int u = 0; u < BATCH; ++u) {
       const double ru = __shfl_sync(full, lo.resid, (u << 2) | q);
 #pragma unroll
       for (int I = 0; I < NB; ++I) gacc[I] = fma(ru, xv[u][I], gacc[I]);
-      if constexpr (HESS) {
+      if constexpr (WANT_U) {
         const double wu = __shfl_sync(full, lo.wgt, (u << 2) | q);
         double af[NB];
 #pragma unroll
         for (int I = 0; I < NB; ++I) { af[I] = wu * xv[u][I]; uacc[I] += af[I]; }
-        int t = 0;
+        if constexpr (HESS) {
+          int t = 0;
 #pragma unroll
-        for (int I = 0; I < NB; ++I)
+          for (int I = 0; I < NB; ++I)
 #pragma unroll
-          for (int J = I; J < NB; ++J) { rg_dmma(acc[t][0], acc[t][1], af[I], xv[u][J]); ++t; }
+            for (int J = I; J < NB; ++J) { rg_dmma(acc[t][0], acc[t][1], af[I], xv[u][J]); ++t; }
+        }
       }
     }
   }
@@ -133,7 +143,7 @@ k_glm_regs(RegsArgs a) {
   for (int I = 0; I < NB; ++I) {
     gacc[I] += __shfl_xor_sync(full, gacc[I], 1);
     gacc[I] += __shfl_xor_sync(full, gacc[I], 2);
-    if constexpr (HESS) {
+    if constexpr (WANT_U) {
       uacc[I] += __shfl_xor_sync(full, uacc[I], 1);
       uacc[I] += __shfl_xor_sync(full, uacc[I], 2);
     }
@@ -164,7 +174,7 @@ k_glm_regs(RegsArgs a) {
         for (int I = 0; I < NB; ++I) {
           double* pg = red + L::G_OFF + 8 * I + g;
           if (first) *pg = gacc[I]; else *pg += gacc[I];
-          if constexpr (HESS) {
+          if constexpr (WANT_U) {
             double* pu = red + L::U_OFF + 8 * I + g;
             if (first) *pu = uacc[I]; else *pu += uacc[I];
           }
@@ -182,10 +192,11 @@ k_glm_regs(RegsArgs a) {
 }
 
 // stats = [H p x p | g p | obj] from the CTA partials, summed in CTA order; H mirrored from its upper triangle
-template <int NB, bool HESS>
+template <int NB, int MODE>
 __global__ void __launch_bounds__(256)
 k_regs_finish(int64_t d, int nparts, const double* __restrict__ parts, double* __restrict__ stats) {
-  using L = RegsLayout<NB, HESS>;
+  using L = RegsLayout<NB, MODE>;
+  constexpr bool HESS = MODE >= 1;                // the intercept column and sum w are part of the result
   constexpr int DD = L::DD;
   const int64_t p = d + 1;
   for (int e = blockIdx.x * 256 + threadIdx.x; e < L::LEN; e += gridDim.x * 256) {
@@ -241,25 +252,25 @@ size_t glm_regs_scratch_bytes(int device, int64_t d, int want_hess) {
   return (size_t)regs_ctas(device) * ((want_hess ? dd * dd : 0) + 2 * dd + 3) * sizeof(double);
 }
 
-template <int NB, bool HESS>
+template <int NB, int MODE>
 static int launch_regs(int device, const RegsArgs& a, double* stats, cudaStream_t st) {
-  using L = RegsLayout<NB, HESS>;
-  const int64_t rows_per_batch = 4 * RegsBatch<NB, HESS>::value;
+  using L = RegsLayout<NB, MODE>;
+  const int64_t rows_per_batch = 4 * RegsBatch<NB, MODE>::value;
   int64_t batches = (a.n + rows_per_batch - 1) / rows_per_batch;
   int64_t want = (batches + RG_WARPS - 1) / RG_WARPS;
   const size_t smem = (size_t)(L::LEN + (NB > 16 ? L::DD : 0)) * sizeof(double);
   // one resident wave: as many CTAs per SM as the kernel's registers allow (the narrow variants need the extra
   // warps to keep enough loads in flight)
   int per_sm = 1;
-  NB_CHECK(cudaFuncSetAttribute(k_glm_regs<NB, HESS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_glm_regs<NB, HESS>, RG_THREADS, smem));
+  NB_CHECK(cudaFuncSetAttribute(k_glm_regs<NB, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_glm_regs<NB, MODE>, RG_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
   if (per_sm > RG_MAX_CTAS_PER_SM) per_sm = RG_MAX_CTAS_PER_SM;
   int ctas = dev_info(device).sms * per_sm;
   if (want < ctas) ctas = (int)(want < 1 ? 1 : want);
-  k_glm_regs<NB, HESS><<<ctas, RG_THREADS, smem, st>>>(a);
+  k_glm_regs<NB, MODE><<<ctas, RG_THREADS, smem, st>>>(a);
   NB_LAUNCH_CHECK();
-  k_regs_finish<NB, HESS><<<(L::LEN + 255) / 256, 256, 0, st>>>(a.d, ctas, a.parts, stats);
+  k_regs_finish<NB, MODE><<<(L::LEN + 255) / 256, 256, 0, st>>>(a.d, ctas, a.parts, stats);
   NB_LAUNCH_CHECK();
   return 0;
 }
@@ -272,16 +283,40 @@ int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d
              "glm_regs_stats: scratch too small");
   RegsArgs a;
   a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.family = family;
+  a.wbuf = nullptr;
   a.parts = (double*)scratch;
   const int nb = regs_nb(d);
-#define RG_CASE(N) case N: return want_hess ? launch_regs<(N <= 8 ? N : 8), true>(device, a, stats, st) \
-                                            : launch_regs<N, false>(device, a, stats, st)
+#define RG_CASE(N) case N: return want_hess ? launch_regs<(N <= 8 ? N : 8), 1>(device, a, stats, st) \
+                                            : launch_regs<N, 0>(device, a, stats, st)
   switch (nb) {
     RG_CASE(1); RG_CASE(2); RG_CASE(3); RG_CASE(4); RG_CASE(5); RG_CASE(6); RG_CASE(7); RG_CASE(8);
     RG_CASE(10); RG_CASE(12); RG_CASE(14); RG_CASE(16); RG_CASE(20); RG_CASE(24);
   }
 #undef RG_CASE
   set_error("glm_regs_stats: no variant for d=%lld", (long long)d);
+  return 2;
+}
+
+// First pass of the two-pass Newton statistics for 64 < d <= 160 (beyond that the accumulators spill): g, u, sum r, sum w, objective into `stats`, the
+// weights into wbuf (null for the linear family, whose weights are 1); glm_fused.cu adds X^T diag(w) X.
+bool glm_regs_pass1_applicable(int64_t d) { return d > 64 && d <= 160 && !getenv("NUMS_B200_NO_REGS"); }
+
+int glm_regs_pass1(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                   const double* beta, double* wbuf, double* stats, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  NB_REQUIRE(glm_regs_pass1_applicable(d), "glm_regs_pass1: d=%lld outside 65..160", (long long)d);
+  NB_REQUIRE(scratch != nullptr && scratch_bytes >= glm_regs_scratch_bytes(device, d, 0), "glm_regs_pass1: scratch too small");
+  RegsArgs a;
+  a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.family = family;
+  a.wbuf = wbuf;
+  a.parts = (double*)scratch;
+  switch (regs_nb(d)) {
+    case 10: return launch_regs<10, 2>(device, a, stats, st);
+    case 12: return launch_regs<12, 2>(device, a, stats, st);
+    case 14: return launch_regs<14, 2>(device, a, stats, st);
+    case 16: return launch_regs<16, 2>(device, a, stats, st);
+    case 20: return launch_regs<20, 2>(device, a, stats, st);
+  }
+  set_error("glm_regs_pass1: no variant for d=%lld", (long long)d);
   return 2;
 }
 
