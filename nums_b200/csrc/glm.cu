@@ -317,9 +317,9 @@ __global__ void __launch_bounds__(256)
 k_glm_rows_finish(int64_t d, int nparts, const double* __restrict__ partials, int want_hess,
                   double* __restrict__ stats) {
   const int64_t p = d + 1, ps = 2 * d + 3;
-  for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < ps; j += (int64_t)gridDim.x * 256) {
-    double s = 0.0;
-    for (int c = 0; c < nparts; c++) s += partials[(size_t)c * ps + j];
+  for (int64_t j = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); j < ps; j += (int64_t)gridDim.x * 8) {   // one warp per statistic
+    const double s = sum_partials_warp(partials + j, (size_t)ps, nparts);
+    if ((threadIdx.x & 31) != 0) continue;
     if (j < d) {
       stats[p * p + j] = s;                               // g[j]
     } else if (j < 2 * d) {
@@ -563,7 +563,7 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
     rc = vec ? launch_rows_cfg<true>(device, a, L.max_parts, &nparts, st)
              : launch_rows_cfg<false>(device, a, L.max_parts, &nparts, st);
   if (rc) return rc;
-  k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 255) / 256), 256, 0, st>>>(d, nparts, parts, want_hess, stats_d);
+  k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, nparts, parts, want_hess, stats_d);
   NB_LAUNCH_CHECK();
   if (tri_ok && glm_mode() == 0) {
     // pass 2: upper-triangular blocks of X^T diag(w) X by FP64 DMMA, mirrored -> exactly symmetric

@@ -6,6 +6,36 @@ namespace nb {
 
 struct LinkOut { double resid, wgt, obj; };
 
+// the same sum by a whole warp (lanes stride over the partials, fixed xor tree): for the short statistics vectors,
+// where one thread per statistic would leave a single CTA walking all the partials
+__device__ __forceinline__ double sum_partials_warp(const double* __restrict__ p, size_t stride, int count) {
+  const int lane = threadIdx.x & 31;
+  double a0 = 0.0, a1 = 0.0;
+  int c = lane;
+  for (; c + 32 < count; c += 64) { a0 += p[(size_t)c * stride]; a1 += p[(size_t)(c + 32) * stride]; }
+  if (c < count) a0 += p[(size_t)c * stride];
+  double s = a0 + a1;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  return s;
+}
+
+// sum_{c < count} p[c * stride] with eight loads in flight and a fixed association (the partials of a pass are summed
+// by one thread per statistic: a serial chain of dependent loads made the finish kernels cost 40-90 us)
+__device__ __forceinline__ double sum_partials(const double* __restrict__ p, size_t stride, int count) {
+  double acc[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  int c = 0;
+  for (; c + 8 <= count; c += 8) {
+    double v[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) v[u] = p[(size_t)(c + u) * stride];
+#pragma unroll
+    for (int u = 0; u < 8; u++) acc[u] += v[u];
+  }
+  for (; c < count; c++) acc[c & 7] += p[(size_t)c * stride];
+  return ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+}
+
 template <int FAMILY>
 __device__ __forceinline__ LinkOut glm_link(double eta, double y) {
   LinkOut o;

@@ -318,8 +318,7 @@ k_fused_finish(const FusedArgs a, double* __restrict__ stats, int h_only) {
       int bi = (int)(i / FB), bj = (int)(j / FB);
       int t = bi * a.nblk - (bi * (bi - 1)) / 2 + (bj - bi);
       const double* src = a.part_h + (size_t)t * (FB * FB) + (i - bi * FB) * FB + (j - bj * FB);
-      double s = 0.0;
-      for (int g = 0; g < a.groups * a.KG; g++) s += src[(size_t)g * a.T * (FB * FB)];
+      const double s = sum_partials(src, (size_t)a.T * (FB * FB), a.groups * a.KG);
       stats[i * p + j] = s;
       stats[j * p + i] = s;
     } else {
@@ -328,8 +327,7 @@ k_fused_finish(const FusedArgs a, double* __restrict__ stats, int h_only) {
       if (q < d) idx = q;                            // g[q]
       else if (q < 2 * d) idx = dp + (q - d);        // u[q - d]
       else idx = 2 * dp + (q - 2 * d);               // sum r, sum w, objective
-      double s = 0.0;
-      for (int g = 0; g < a.groups * a.C; g++) s += a.part_v[(size_t)g * (2 * dp + 3) + idx];
+      const double s = sum_partials(a.part_v + idx, (size_t)(2 * dp + 3), a.groups * a.C);
       if (q < d) stats[p * p + q] = s;
       else if (q < 2 * d) { int64_t i = q - d; stats[i * p + d] = s; stats[d * p + i] = s; }
       else if (q == 2 * d) stats[p * p + d] = s;

@@ -199,7 +199,11 @@ k_regs_finish(int64_t d, int nparts, const double* __restrict__ parts, double* _
   constexpr bool HESS = MODE >= 1;                // the intercept column and sum w are part of the result
   constexpr int DD = L::DD;
   const int64_t p = d + 1;
-  for (int e = blockIdx.x * 256 + threadIdx.x; e < L::LEN; e += gridDim.x * 256) {
+  // short vectors: one warp per statistic; with the tile area: one thread per statistic
+  constexpr bool WARP_EACH = L::LEN <= 2048;
+  const int first = WARP_EACH ? blockIdx.x * 8 + (threadIdx.x >> 5) : blockIdx.x * 256 + threadIdx.x;
+  const int step = WARP_EACH ? gridDim.x * 8 : gridDim.x * 256;
+  for (int e = first; e < L::LEN; e += step) {
     int i = 0, j = 0;
     if (e < L::G_OFF) {
       // tiles on the diagonal hold both halves (computed with different roundings): only the upper one is used
@@ -211,8 +215,9 @@ k_regs_finish(int64_t d, int nparts, const double* __restrict__ parts, double* _
     } else if (e == L::S_OFF + 1 && !HESS) {
       continue;
     }
-    double s = 0.0;
-    for (int c = 0; c < nparts; ++c) s += parts[(size_t)c * L::LEN + e];
+    const double s = WARP_EACH ? sum_partials_warp(parts + e, (size_t)L::LEN, nparts)
+                               : sum_partials(parts + e, (size_t)L::LEN, nparts);
+    if (WARP_EACH && (threadIdx.x & 31) != 0) continue;
     if (e < L::G_OFF) {
       stats[i * p + j] = s;
       stats[j * p + i] = s;
@@ -270,7 +275,7 @@ static int launch_regs(int device, const RegsArgs& a, double* stats, cudaStream_
   if (want < ctas) ctas = (int)(want < 1 ? 1 : want);
   k_glm_regs<NB, MODE><<<ctas, RG_THREADS, smem, st>>>(a);
   NB_LAUNCH_CHECK();
-  k_regs_finish<NB, MODE><<<(L::LEN + 255) / 256, 256, 0, st>>>(a.d, ctas, a.parts, stats);
+  k_regs_finish<NB, MODE><<<L::LEN <= 2048 ? (L::LEN + 7) / 8 : (L::LEN + 255) / 256, 256, 0, st>>>(a.d, ctas, a.parts, stats);
   NB_LAUNCH_CHECK();
   return 0;
 }
