@@ -104,11 +104,9 @@ def read_csv_block(filename, file_start, file_end, dtype, delimiter, has_header,
     st = dv.stream_ptr(dev)
     text = dv.upload_bytes(data, dev)
     rows_c = C.c_int64(0)
-    sc = dv.scratch(lib.nb_csv_scratch_bytes(len(data), 0), dev)
+    sc = dv.scratch(lib.nb_csv_scratch_bytes(len(data), data.count(b"\n")), dev)   # sized by a host memchr pass
     _lib.check(lib.nb_csv_count_rows(dev, text.data_ptr(), len(data), sc.data_ptr(), sc.numel(), C.byref(rows_c), st))
     rows = int(rows_c.value)
-    sc = dv.scratch(lib.nb_csv_scratch_bytes(len(data), rows), dev)
-    _lib.check(lib.nb_csv_count_rows(dev, text.data_ptr(), len(data), sc.data_ptr(), sc.numel(), C.byref(rows_c), st))
     out = dv.empty((rows, cols), np_dtype, dev)
     err = (C.c_int64 * 3)()
     _lib.check(lib.nb_csv_parse(dev, text.data_ptr(), len(data), rows, cols, delimiter.encode()[0], out.code, out.ptr,
