@@ -334,6 +334,18 @@ k_glm_rows_finish(int64_t d, int nparts, const double* __restrict__ partials, in
   }
 }
 
+// mu[i] = link_inv(mu[i] + beta0)
+__global__ void __launch_bounds__(256)
+k_glm_link_inplace(int family, int64_t n, const double* __restrict__ beta0, double* __restrict__ mu) {
+  const double b0 = *beta0;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
+    const double eta = mu[i] + b0;
+    mu[i] = (family == NB_GLM_LOGISTIC || family == NB_GLM_LOGISTIC_IRLS) ? glm_mu<NB_GLM_LOGISTIC>(eta)
+          : (family == NB_GLM_POISSON ? glm_mu<NB_GLM_POISSON>(eta) : eta);
+  }
+}
+
 // mu = link_inv(X beta + beta0), one warp per row
 __global__ void __launch_bounds__(GLM_THREADS)
 k_glm_predict(int family, const double* __restrict__ x, int64_t n, int64_t d, int64_t ldx,
@@ -349,7 +361,7 @@ k_glm_predict(int family, const double* __restrict__ x, int64_t n, int64_t d, in
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if (lane == 0) {
       double eta = s + b0;
-      mu[r] = family == NB_GLM_LOGISTIC ? glm_mu<NB_GLM_LOGISTIC>(eta)
+      mu[r] = (family == NB_GLM_LOGISTIC || family == NB_GLM_LOGISTIC_IRLS) ? glm_mu<NB_GLM_LOGISTIC>(eta)
             : (family == NB_GLM_POISSON ? glm_mu<NB_GLM_POISSON>(eta) : eta);
     }
   }
@@ -583,6 +595,15 @@ int nb_glm_predict(int device, int family, const double* x_d, int64_t n, int64_t
                    const double* beta_d, double* mu_d, void* stream) {
   NB_ENTER(device);
   if (n == 0) return 0;
+  if (d <= 512 && (d & 1) == 0 && (ldx & 1) == 0 && n >= 256 && ((((uintptr_t)x_d) | ((uintptr_t)beta_d)) & 15) == 0) {
+    // narrow rows: eta by the sub-warp mat-vec (16-byte loads, several rows per warp), then the link in place
+    int rc = gemm_f64(device, n, 1, d, x_d, ldx, 1, beta_d, 1, 1, nullptr, mu_d, 1, nullptr, 0, st);
+    if (rc) return rc;
+    const int grid = grid_for(device, n, 256, 4);
+    k_glm_link_inplace<<<grid, 256, 0, st>>>(family, n, beta_d + d, mu_d);
+    NB_LAUNCH_CHECK();
+    return 0;
+  }
   int64_t blocks = (n + 7) / 8;
   int64_t cap = (int64_t)dev_info(device).sms * 8;
   k_glm_predict<<<(unsigned)(blocks < cap ? blocks : cap), GLM_THREADS, 0, st>>>(family, x_d, n, d, ldx, beta_d, mu_d);

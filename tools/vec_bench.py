@@ -44,3 +44,9 @@ ci = dv.from_numpy(np.int64(3), 0)
 show("x == c  (int64 -> bool, 1e8)", timeit(lambda: K.bop("eq", xi, ci, False, False, {})), 9 * n)
 show("x < y   (f64, f64 -> bool, 1e8)", timeit(lambda: K.bop("lt", x, x, False, False, {})), 17 * n)
 show("argmax int64 1e8", timeit(lambda: K.arg_op("argmax", xi, slice(0, n))), 8 * n)
+from nums_b200 import fused
+for d in (8, 64, 256):
+    rows = n // d
+    X = dv.DeviceBlock(x.t[: rows * d].view(rows, d))
+    bfull = dv.from_numpy(rng.standard_normal(d + 1) * 0.1, 0)
+    show("glm_predict logistic (%d x %d)" % (rows, d), timeit(lambda: fused.glm_predict(X, bfull, "logistic")), 8 * rows * d + 8 * rows)
