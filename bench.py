@@ -254,7 +254,7 @@ def run_ours(args, result):
     sc = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 1), local)
 
     def gram():
-        _lib.check(lib.nb_glm_stats(local, 1, X.ptr, n, d, d, y.ptr, y.code, beta_d.ptr, 1, stats_d.ptr,
+        _lib.check(lib.nb_glm_stats(local, 1, X.ptr, n, d, d, y.ptr, y.code, beta_d.ptr, 3, stats_d.ptr,
                                     sc.data_ptr(), sc.numel(), st))
 
     for _ in range(3):
@@ -397,7 +397,7 @@ def run_ours(args, result):
                  "achieved_tflops_executed": executed_flops / (tri_ms * 1e-3) / 1e12,
                  "peak_tflops": fp64_peak,
                  "frac_executed": (executed_flops / (tri_ms * 1e-3) / 1e12 / fp64_peak) if fp64_peak else None},
-        "stats_pass": {"what": "nb_glm_stats(want_hess=1) = pass 1 + pass 2 + finish kernels", "ms_per_launch": gram_ms,
+        "stats_pass": {"what": "nb_glm_stats(NB_GLM_HESS_NO_OBJECTIVE), what a Newton step runs = pass 1 + pass 2 + finish kernels", "ms_per_launch": gram_ms,
                        "achieved": gram_bytes / (gram_ms * 1e-3) / 1e9, "unit": "GB/s"},
         "pass1": {"kernel": "k_glm_rows (eta/link/objective/gradient, HBM-bound)", "ms_per_launch": rows_ms,
                   "achieved": gram_bytes / (rows_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",

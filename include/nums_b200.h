@@ -287,8 +287,12 @@ int nb_svd_f64(int device, int64_t p, const double* a_d, double* u_d, double* s_
  *     H    = [X,1]^T diag(w) [X,1], w = mu(1-mu) | 1 | mu  (stats_d[0 .. p*p), row-major)
  * into ONE packed buffer stats_d of nb_glm_stats_len(d) doubles, so a single all-reduce sums
  * the row shards.  want_hess == 0 skips H (L-BFGS / gradient passes) and leaves that part of
- * stats_d untouched.  Penalty terms are not included (they are added once, after the
+ * stats_d untouched.  want_hess == NB_GLM_HESS_NO_OBJECTIVE (3) computes g and H but not the
+ * objective, whose slot is set to 0: newton() (glms.py:660-676) never evaluates it, and its two
+ * logarithms per row are most of the link's cost on narrow blocks (d <= 7 always computes it).
+ * Penalty terms are not included (they are added once, after the
  * all-reduce, by nb_glm_newton_update or the host).  Deterministic. */
+#define NB_GLM_HESS_NO_OBJECTIVE 3
 int64_t nb_glm_stats_len(int64_t d);
 size_t nb_glm_scratch_bytes(int device, int64_t n, int64_t d, int want_hess);
 int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx,

@@ -120,6 +120,7 @@ struct GlmRowsArgs {
   const void* y; int ydt;
   const double* beta;
   int family, want_hess;
+  int skip_obj;        // Newton does not read the objective: leave out its two logarithms per row
   double* wbuf;        // n weights for pass 2 (null: not needed)
   double* partials;    // [gridDim.x][2*d + 3]
 };
@@ -265,7 +266,8 @@ k_glm_rows(const GlmRowsArgs a) {
     eta += beta0;
     const int64_t myrow = row0 + (lane % R);
     const bool inb = myrow < n;
-    LinkOut lo = glm_link_rt(a.family, eta, inb ? load_y(a.y, a.ydt, myrow) : 0.0);
+    const double yv = inb ? load_y(a.y, a.ydt, myrow) : 0.0;
+    LinkOut lo = a.skip_obj ? glm_link_noobj_rt(a.family, eta, yv) : glm_link_rt(a.family, eta, yv);
     if (!inb) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
     if (wc == 0 && lane < R && inb) {
       ob += lo.obj; gi += lo.resid; ui += lo.wgt;
@@ -376,11 +378,12 @@ static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 bool glm_regs_applicable(int64_t d, int want_hess);
 size_t glm_regs_scratch_bytes(int device, int64_t d, int want_hess);
 int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
-                   const double* beta, int want_hess, double* stats, void* scratch, size_t scratch_bytes,
+                   const double* beta, int want_hess, int skip_obj, double* stats, void* scratch, size_t scratch_bytes,
                    cudaStream_t st);
 bool glm_regs_pass1_applicable(int64_t d);
 int glm_regs_pass1(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
-                   const double* beta, double* wbuf, double* stats, void* scratch, size_t scratch_bytes, cudaStream_t st);
+                   const double* beta, int skip_obj, double* wbuf, double* stats, void* scratch, size_t scratch_bytes,
+                   cudaStream_t st);
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
 int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
@@ -522,7 +525,7 @@ extern "C" {
 int64_t nb_glm_stats_len(int64_t d) { int64_t p = d + 1; return p * p + p + 1; }
 
 size_t nb_glm_scratch_bytes(int device, int64_t n, int64_t d, int want_hess) {
-  return glm_layout(device, n, d, want_hess).total;
+  return glm_layout(device, n, d, want_hess & 1).total;
 }
 
 int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx, const void* y_d,
@@ -533,6 +536,8 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   NB_REQUIRE(d >= 1 && n >= 0 && ldx >= d, "nb_glm_stats: bad shape n=%lld d=%lld ldx=%lld", (long long)n,
              (long long)d, (long long)ldx);
   NB_REQUIRE(ydt == NB_F64 || ydt == NB_I64, "nb_glm_stats: y dtype %d not supported", ydt);
+  const int skip_obj = (want_hess & 2) ? 1 : 0;      // NB_GLM_NO_OBJECTIVE
+  want_hess &= 1;
   GlmLayout L = glm_layout(device, n, d, want_hess);
   NB_REQUIRE(scratch_d != nullptr && scratch_bytes >= L.total, "nb_glm_stats: scratch too small (%zu < %zu)",
              scratch_bytes, L.total);
@@ -547,14 +552,14 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
     }
   }
   if (glm_regs_applicable(d, want_hess))
-    return glm_regs_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, stats_d, sc, L.total, st);
+    return glm_regs_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, skip_obj, stats_d, sc, L.total, st);
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);
   if (tri_ok && glm_mode() == 1)
     return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, nullptr, true, stats_d, d + 1,
                            sc + L.off_gemm, L.total - L.off_gemm, st);
   GlmRowsArgs a;
   a.x = x_d; a.n = n; a.d = d; a.ldx = ldx; a.y = y_d; a.ydt = ydt; a.beta = beta_d;
-  a.family = family; a.want_hess = want_hess;
+  a.family = family; a.want_hess = want_hess; a.skip_obj = skip_obj;
   const bool need_w = want_hess && family != NB_GLM_LINEAR;
   a.wbuf = need_w ? (double*)(sc + L.off_w) : nullptr;
   a.partials = parts;
@@ -563,7 +568,7 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   int rc;
   if (tri_ok && glm_mode() == 0 && glm_regs_pass1_applicable(d)) {
     // 64 < d <= 192: the register-resident kernel is the faster first pass (its partials live in the parts region)
-    rc = glm_regs_pass1(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, stats_d, parts,
+    rc = glm_regs_pass1(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, skip_obj, a.wbuf, stats_d, parts,
                         L.off_gemm - L.off_parts, st);
     if (rc) return rc;
     return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, false, stats_d, d + 1,

@@ -32,6 +32,7 @@ struct RegsArgs {
   const void* y; int ydt;
   const double* beta;
   int family;
+  int skip_obj;       // the objective is not needed (Newton): its two logarithms per row are left out
   double* wbuf;       // mode 2: the Hessian weights w (n doubles) for the second pass, or null
   double* parts;      // per CTA: [dd*dd tiles | g dd | u dd | sum r | sum w | obj]
 };
@@ -113,7 +114,7 @@ k_glm_regs(RegsArgs a) {
       eta += __shfl_xor_sync(full, eta, 16);
       if (u == gl) my_eta = eta;
     }
-    LinkOut lo = glm_link_rt(a.family, my_eta + b0, yv);
+    LinkOut lo = a.skip_obj ? glm_link_noobj_rt(a.family, my_eta + b0, yv) : glm_link_rt(a.family, my_eta + b0, yv);
     if (!live) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
     sr += lo.resid; sobj += lo.obj;
     if constexpr (WANT_U) sw += lo.wgt;
@@ -281,7 +282,7 @@ static int launch_regs(int device, const RegsArgs& a, double* stats, cudaStream_
 }
 
 int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
-                   const double* beta, int want_hess, double* stats, void* scratch, size_t scratch_bytes,
+                   const double* beta, int want_hess, int skip_obj, double* stats, void* scratch, size_t scratch_bytes,
                    cudaStream_t st) {
   NB_REQUIRE(glm_regs_applicable(d, want_hess), "glm_regs_stats: d=%lld outside the register-resident range", (long long)d);
   NB_REQUIRE(scratch != nullptr && scratch_bytes >= glm_regs_scratch_bytes(device, d, want_hess),
@@ -289,6 +290,7 @@ int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d
   RegsArgs a;
   a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.family = family;
   a.wbuf = nullptr;
+  a.skip_obj = skip_obj;
   a.parts = (double*)scratch;
   const int nb = regs_nb(d);
 #define RG_CASE(N) case N: return want_hess ? launch_regs<(N <= 8 ? N : 8), 1>(device, a, stats, st) \
@@ -307,12 +309,14 @@ int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d
 bool glm_regs_pass1_applicable(int64_t d) { return d > 64 && d <= 160 && !getenv("NUMS_B200_NO_REGS"); }
 
 int glm_regs_pass1(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
-                   const double* beta, double* wbuf, double* stats, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+                   const double* beta, int skip_obj, double* wbuf, double* stats, void* scratch, size_t scratch_bytes,
+                   cudaStream_t st) {
   NB_REQUIRE(glm_regs_pass1_applicable(d), "glm_regs_pass1: d=%lld outside 65..160", (long long)d);
   NB_REQUIRE(scratch != nullptr && scratch_bytes >= glm_regs_scratch_bytes(device, d, 0), "glm_regs_pass1: scratch too small");
   RegsArgs a;
   a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.family = family;
   a.wbuf = wbuf;
+  a.skip_obj = skip_obj;
   a.parts = (double*)scratch;
   switch (regs_nb(d)) {
     case 10: return launch_regs<10, 2>(device, a, stats, st);

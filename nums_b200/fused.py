@@ -11,8 +11,9 @@ from . import hostlogic as hl
 from .device import DeviceBlock
 
 
-def glm_stats(x, y, beta, family, want_hess):
-    """Packed [H (p*p) | g (p) | objective (1)] of one row block (see nb_glm_stats)."""
+def glm_stats(x, y, beta, family, want_hess, need_obj=True):
+    """Packed [H (p*p) | g (p) | objective (1)] of one row block (see nb_glm_stats).  need_obj=False (with
+    want_hess) leaves the objective out: the Newton loop never reads it."""
     lib = _lib.load()
     dev = x.device_index
     if x.ndim != 2 or x.dtype != np.dtype(np.float64):
@@ -30,8 +31,9 @@ def glm_stats(x, y, beta, family, want_hess):
     if not want_hess:   # the H part is not written by the kernel: keep the buffer defined for the all-reduce
         _lib.check(lib.nb_fill(dev, out.size, out.ptr, out.code, 0.0, 0, dv.stream_ptr(dev)))
     sc = dv.scratch(lib.nb_glm_scratch_bytes(dev, n, d, int(bool(want_hess))), dev)
+    mode = 3 if (want_hess and not need_obj) else int(bool(want_hess))      # 3 = NB_GLM_HESS_NO_OBJECTIVE
     _lib.check(lib.nb_glm_stats(dev, hl.FAMILY_CODE[family], x.ptr, n, d, x.strides[0], y.ptr, y.code, beta.ptr,
-                                int(bool(want_hess)), out.ptr, sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+                                mode, out.ptr, sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
     return out
 
 

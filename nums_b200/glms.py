@@ -165,7 +165,7 @@ class GLM:
         dist.all_reduce(stats_oid.t, op=dist.ReduceOp.SUM)
         return stats_oid
 
-    def fused_stats(self, X, y, beta, want_hess, family=None):
+    def fused_stats(self, X, y, beta, want_hess, family=None, need_obj=True):
         """Sum over all row blocks (and ranks) of the packed statistics at `beta` (single block)."""
         km = self._app.km
         family = self.family if family is None else family
@@ -175,7 +175,7 @@ class GLM:
             xb, yb = X.blocks[(i, 0)], y.blocks[(i,)]
             if xb.transposed:
                 raise NotImplementedError("fused path on a transposed X")
-            oid = km.call("glm_stats", xb.oid, yb.oid, b_oid, family, want_hess, syskwargs=xb.syskwargs())
+            oid = km.call("glm_stats", xb.oid, yb.oid, b_oid, family, want_hess, need_obj, syskwargs=xb.syskwargs())
             items.append((oid, xb.grid_entry, xb.grid_shape, False))
         total = X.tree_reduce("sum", items, (0,), (1,))
         return self._allreduce(total)
@@ -454,7 +454,7 @@ def newton(model, beta, X, y, tol, max_iter):
         sk = {"grid_entry": (0,), "grid_shape": (1,)}
         p = beta.shape[0]
         for _ in range(max_iter):
-            stats = model.fused_stats(X, y, beta, True)
+            stats = model.fused_stats(X, y, beta, True, need_obj=False)     # newton() never evaluates the objective
             if model._l1penalty_vec is not None and not poisson_skip:
                 # the L1 term of grad_penalty (glms.py:254-264) is added to g before the update; its Hessian
                 # contribution is zero (:266-272)

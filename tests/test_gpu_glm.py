@@ -236,6 +236,23 @@ def test_register_resident_gradient_pass_wide(app, family, d):
         assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
 
 
+@pytest.mark.parametrize("d", [5, 16, 64, 100, 256, 300])
+def test_newton_statistics_without_the_objective(app, d):
+    """NB_GLM_HESS_NO_OBJECTIVE (what newton() asks for): identical g and H, objective slot 0."""
+    from nums_b200 import device as dv, fused
+    rng = np.random.default_rng(d)
+    n = 8_000 + d
+    X = dv.from_numpy(rng.standard_normal((n, d)) / np.sqrt(d), 0)
+    y = dv.from_numpy((rng.random(n) < 0.5).astype(np.int64), 0)
+    beta = dv.from_numpy(rng.standard_normal(d + 1) * 0.3, 0)
+    for family in ("logistic", "poisson"):
+        full = dv.to_numpy(fused.glm_stats(X, y, beta, family, True))
+        lean = dv.to_numpy(fused.glm_stats(X, y, beta, family, True, need_obj=False))
+        p = d + 1
+        assert np.array_equal(full[: p * p + p], lean[: p * p + p])
+        assert lean[p * p + p] == 0.0 or d <= 7        # d <= 7 always computes it
+
+
 def test_glm_edge_cases(app):
     """ragged last block, a single row, and an empty row block"""
     from nums_b200.glms import LogisticRegression
