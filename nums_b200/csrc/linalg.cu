@@ -23,6 +23,7 @@ struct InvArgs {
   double* slot_v;   // [2][G] pivot candidates: |value|
   int* slot_r;      // [2][G] pivot candidates: logical row
   int32_t* info;
+  const int* gate;  // null: always run; else run only when *gate != 0 (fallback of the Cholesky Newton step)
 };
 
 template <bool COOP>
@@ -65,6 +66,7 @@ template <bool COOP>
 __global__ void __launch_bounds__(INV_THREADS)
 k_inv(const InvArgs a) {
   extern __shared__ __align__(16) unsigned char inv_smem[];
+  if (a.gate != nullptr && *a.gate == 0) return;        // uniform over the grid, before any barrier
   const int p = (int)a.p;
   const int G = COOP ? (int)gridDim.x : 1;
   const int b = COOP ? (int)blockIdx.x : 0;
@@ -186,7 +188,7 @@ static size_t inv_scratch(int64_t p) {
 }
 
 static int inv_f64(int device, int64_t p, const double* a_in, double* out, int32_t* info, void* scratch,
-                   size_t scratch_bytes, cudaStream_t st) {
+                   size_t scratch_bytes, cudaStream_t st, const int* gate = nullptr) {
   NB_REQUIRE(p >= 1 && p <= INV_MAX_P, "inv: p=%lld outside 1..%lld", (long long)p, (long long)INV_MAX_P);
   NB_REQUIRE(scratch != nullptr && scratch_bytes >= inv_scratch(p), "inv: scratch too small (%zu < %zu)",
              scratch_bytes, inv_scratch(p));
@@ -197,6 +199,7 @@ static int inv_f64(int device, int64_t p, const double* a_in, double* out, int32
   a.slot_r = (int*)((char*)a.slot_v + align256(2 * 1024 * sizeof(double)));
   a.out = out;
   a.info = info;
+  a.gate = gate;
   NB_CHECK(cudaMemcpyAsync(a.a, a_in, (size_t)p * p * sizeof(double), cudaMemcpyDeviceToDevice, st));
   const bool coop = p > 32;
   int G = 1;
@@ -256,7 +259,8 @@ k_newton_prep(int64_t p, double* __restrict__ stats, const double* __restrict__ 
 // beta_out = beta - Hinv @ g, one warp per row
 __global__ void __launch_bounds__(256)
 k_newton_apply(int64_t p, const double* __restrict__ hinv, const double* __restrict__ g,
-               const double* __restrict__ beta, double* __restrict__ beta_out) {
+               const double* __restrict__ beta, double* __restrict__ beta_out, const int* __restrict__ gate) {
+  if (gate != nullptr && *gate == 0) return;
   const int lane = threadIdx.x & 31;
   const int64_t warps = (int64_t)gridDim.x * 8;
   for (int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); i < p; i += warps) {
@@ -267,6 +271,10 @@ k_newton_apply(int64_t p, const double* __restrict__ hinv, const double* __restr
     if (lane == 0) beta_out[i] = beta[i] - s;
   }
 }
+
+// newton_chol.cu
+int newton_chol_solve(int device, int64_t p, const double* h, double* l, const double* g, const double* beta,
+                      double* beta_out, double* z, int* flag, int32_t* info, cudaStream_t st);
 
 }  // namespace nb
 
@@ -283,7 +291,7 @@ int nb_inv_f64(int device, int64_t p, const double* a_d, double* out_d, int32_t*
 }
 
 size_t nb_glm_newton_scratch_bytes(int64_t p) {
-  return inv_scratch(p) + align256((size_t)p * p * sizeof(double));
+  return inv_scratch(p) + align256((size_t)p * p * sizeof(double)) + align256((size_t)p * sizeof(double)) + 256;
 }
 
 int nb_glm_newton_update(int device, int64_t p, double* stats_d, const double* l2vec_d, const double* beta_d,
@@ -292,14 +300,27 @@ int nb_glm_newton_update(int device, int64_t p, double* stats_d, const double* l
   NB_ENTER(device);
   NB_REQUIRE(scratch_d != nullptr && scratch_bytes >= nb_glm_newton_scratch_bytes(p),
              "nb_glm_newton_update: scratch too small (%zu < %zu)", scratch_bytes, nb_glm_newton_scratch_bytes(p));
+  // scratch: [hinv / Cholesky factor p*p | z p | flag | inverse scratch]
   double* hinv = (double*)scratch_d;
-  void* inv_sc = (char*)scratch_d + align256((size_t)p * p * sizeof(double));
+  char* sp = (char*)scratch_d + align256((size_t)p * p * sizeof(double));
+  double* z = (double*)sp; sp += align256((size_t)p * sizeof(double));
+  int* flag = (int*)sp; sp += 256;
+  void* inv_sc = sp;
+  const size_t inv_bytes = scratch_bytes - (size_t)(sp - (char*)scratch_d);
   k_newton_prep<<<1, 256, 0, st>>>(p, stats_d, l2vec_d, beta_d, gmax_d);
   NB_LAUNCH_CHECK();
-  int rc = inv_f64(device, p, stats_d, hinv, info_d, inv_sc, scratch_bytes - align256((size_t)p * p * sizeof(double)), st);
+  const int* gate = nullptr;
+  if (p >= 2 && !getenv("NUMS_B200_NEWTON_INVERSE")) {
+    // H = L L^T, two substitutions (newton_chol.cu); the pivoted inverse below runs only if H is not positive definite
+    int rc = newton_chol_solve(device, p, stats_d, hinv, stats_d + p * p, beta_d, beta_out_d, z, flag, info_d, st);
+    if (rc) return rc;
+    gate = flag;
+  }
+  int rc = inv_f64(device, p, stats_d, hinv, info_d, inv_sc, inv_bytes, st, gate);
   if (rc) return rc;
   int64_t blocks = (p + 7) / 8;
-  k_newton_apply<<<(unsigned)(blocks < 1184 ? blocks : 1184), 256, 0, st>>>(p, hinv, stats_d + p * p, beta_d, beta_out_d);
+  k_newton_apply<<<(unsigned)(blocks < 1184 ? blocks : 1184), 256, 0, st>>>(p, hinv, stats_d + p * p, beta_d, beta_out_d,
+                                                                           gate);
   NB_LAUNCH_CHECK();
   return 0;
 }
