@@ -7,7 +7,7 @@
 //   per 32-column panel: CTA 0 factorises the diagonal block in shared memory (one warp) | every thread solves one row
 //   of the panel against it | the trailing lower triangle takes its rank-32 update;
 //   then CTA 0 runs the two blocked substitutions and writes beta_out.
-// If a pivot is not positive (H not positive definite: unpenalised separable data, a singular design) the kernel sets
+// If a pivot is not safely positive (H not positive definite: unpenalised separable data, a singular design) the kernel sets
 // *flag and leaves everything else untouched; the caller's pivoted inverse path is gated on that flag, so the result
 // is then exactly the old one.  Sums run in a fixed order: deterministic.
 #include "common.cuh"
@@ -58,7 +58,10 @@ k_chol_solve(const CholArgs a) {
         int bad = 0;
         for (int j = 0; j < nb; ++j) {
           const double djj = sb[j][j];
-          if (!(djj > 0.0)) { bad = j + 1; break; }          // uniform: every lane reads the same value
+          // a pivot that cancelled down to rounding noise (exactly singular H: LU would meet a zero pivot) is not
+          // trusted either: the pivoted inverse decides such cases, as it did before.  Uniform over the warp.
+          const double orig = a.h[(size_t)(k0 + j) * p + k0 + j];
+          if (!(djj > 1e-13 * fabs(orig))) { bad = j + 1; break; }
           const double r = sqrt(djj);
           __syncwarp();
           if (lane == j) sb[j][j] = r;

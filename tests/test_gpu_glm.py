@@ -253,6 +253,41 @@ def test_newton_statistics_without_the_objective(app, d):
         assert lean[p * p + p] == 0.0 or d <= 7        # d <= 7 always computes it
 
 
+@pytest.mark.parametrize("p", [2, 3, 31, 32, 33, 65, 257, 300, 1025])
+def test_newton_update_cholesky_step_and_its_fallback(app, p):
+    """nb_glm_newton_update: beta - H^-1 g (glms.py:660-676).  A positive definite H takes the blocked Cholesky solve
+    (csrc/newton_chol.cu), an indefinite one the pivoted inverse behind it, a singular one reports info != 0."""
+    from nums_b200 import device as dv, fused
+    rng = np.random.default_rng(p)
+    A = rng.standard_normal((p + 3, p))
+    H = A.T @ A + 0.5 * np.eye(p)
+    g, beta, l2 = rng.standard_normal(p), rng.standard_normal(p), np.abs(rng.standard_normal(p))
+    l2[-1] = 0.0
+
+    def run(Hm, with_l2):
+        stats = dv.from_numpy(np.concatenate([Hm.reshape(-1), g, [0.0]]), 0)
+        out, gmax, info = fused.glm_newton_update(stats, dv.from_numpy(l2, 0) if with_l2 else None, dv.from_numpy(beta, 0))
+        return dv.to_numpy(out), float(dv.to_numpy(gmax)), int(dv.to_numpy(info)[0])
+
+    for with_l2 in (False, True):
+        Hp = H + (np.diag(l2) if with_l2 else 0.0)
+        gp = g + (l2 * beta if with_l2 else 0.0)
+        out, gmax, info = run(H, with_l2)
+        assert info == 0 and abs(gmax - np.max(np.abs(gp))) <= 1e-14 * np.max(np.abs(gp))
+        assert rel_err(out, beta - np.linalg.solve(Hp, gp)) < 1e-10
+    # indefinite but regular: the Cholesky pivot fails, the pivoted inverse gives the reference's step
+    Hi = H.copy()
+    Hi[0, 0] = -abs(Hi[0, 0]) - 1.0
+    out, _, info = run(Hi, False)
+    assert info == 0 and rel_err(out, beta - np.linalg.inv(Hi) @ g) < 1e-9
+    # singular (two equal rows and columns): reported, as np.linalg.inv raises in the reference
+    Hs = H.copy()
+    Hs[1, :] = Hs[0, :]
+    Hs[:, 1] = Hs[:, 0]
+    Hs[1, 1] = Hs[0, 0]
+    assert run(Hs, False)[2] != 0
+
+
 def test_glm_edge_cases(app):
     """ragged last block, a single row, and an empty row block"""
     from nums_b200.glms import LogisticRegression
