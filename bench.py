@@ -403,7 +403,9 @@ def run_ours(args, result):
                   "achieved": gram_bytes / (rows_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                   "frac": gram_bytes / (rows_ms * 1e-3) / 1e9 / hbm_peak},
         "clocks": clocks,
-        "gpu_launches": 7 * K,
+        # per Newton step: k_glm_rows, k_glm_rows_finish, k_tri_gram, k_fused_finish, k_newton_prep, k_chol_solve, and the
+        # gated fallback pair k_inv / k_newton_apply (launched, exit at once when the Cholesky step succeeded)
+        "gpu_launches": 8 * K,
         "coef_checksum": float(np.sum(np.abs(km.get(beta.blocks[(0,)].oid)))),
     }
     if e2e is not None:
