@@ -11,6 +11,8 @@ synchronisation point, like `ray.get`.
 When the real `nums` package is importable this class derives from its `Backend`; otherwise from a
 local stand-in with the same 12 methods, so the plug-in also runs where NumS itself is absent.
 """
+import sys
+
 import numpy as np
 
 from . import device as dv
@@ -65,6 +67,8 @@ class CudaBackend(_BackendBase):
         if any(i < 0 or i >= visible for i in self._device_ids):
             raise RuntimeError("device_ids %s out of range (%d visible)" % (self._device_ids, visible))
         dev_cls = _NumsDevice if _NumsDevice is not None else Device
+        if dev_cls is Device and "nums.core.grid.grid" in sys.modules:   # NumS imported after this module
+            dev_cls = sys.modules["nums.core.grid.grid"].Device
         self._devices = [dev_cls(0, "localhost", "gpu", g) for g in range(self.num_gpus)]
 
     def shutdown(self):
@@ -94,8 +98,14 @@ class CudaBackend(_BackendBase):
         return HostObject(value)
 
     def get(self, object_ids):
-        if isinstance(object_ids, (list, tuple)):
+        if isinstance(object_ids, list):
             return [self.get(o) for o in object_ids]
+        if isinstance(object_ids, tuple):
+            # a tuple of oids (multi-return) is fetched element-wise; a plain tuple (e.g. the shape `where` returns,
+            # application.py:634) is a value and comes back as it is
+            if any(isinstance(o, (DeviceBlock, HostObject)) for o in object_ids):
+                return tuple(self.get(o) for o in object_ids)
+            return object_ids
         if isinstance(object_ids, DeviceBlock):
             arr = dv.to_numpy(object_ids)
             return arr[()] if arr.ndim == 0 else arr

@@ -68,8 +68,174 @@ def _unsupported(name):
     raise NotImplementedError(
         "KernelCls.%s is outside the B200 hot path (SURVEY.md section 8) and has no device implementation" % name)
 
+# Helpers live at module level: NumS registers EVERY bound method of KernelCls() as a remote function and looks
+# each one up in the Kernel interface (kernel_manager.py:76-84), so the class may hold interface methods only.
+def _stream_state(rng_params):
+    """NumPy seeds and jumps the bit generator (SeedSequence + PCG64.jumped stay on the host); the device gets
+    the block's 128-bit LCG state and increment as {hi, lo} pairs."""
+    seed, jump = rng_params
+    st = PCG64(seed).jumped(jump).state["state"]
+    mask = (1 << 64) - 1
+    return ((C.c_uint64 * 2)(st["state"] >> 64, st["state"] & mask),
+            (C.c_uint64 * 2)(st["inc"] >> 64, st["inc"] & mask))
+
+
+def _random_on_device(K, rng_params, size, shape, dev):
+    """Uniform doubles generated in HBM, bit-identical to the host stream (nb_pcg64_random)."""
+    state, inc = _stream_state(rng_params)
+    out = dv.empty((size,), np.float64, dev)
+    _lib.check(_lib.load().nb_pcg64_random(dev, size, state, inc, out.ptr, dv.stream_ptr(dev)))
+    return DeviceBlock(out.t.view(tuple(shape)))
+
+
+def _normal_on_device(K, rng_params, size, shape, dev, loc, scale, standard):
+    """Generator.normal / standard_normal in HBM, in the host generator's order (nb_pcg64_normal)."""
+    lib = _lib.load()
+    state, inc = _stream_state(rng_params)
+    out = dv.empty((size,), np.float64, dev)
+    sc = dv.scratch(lib.nb_pcg64_normal_scratch_bytes(size), dev)
+    _lib.check(lib.nb_pcg64_normal(dev, size, state, inc, loc, scale, 1 if standard else 0, out.ptr,
+                                   sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+    return DeviceBlock(out.t.view(tuple(shape)))
+
+
+def _integers_on_device(K, rng_params, low, high, size, endpoint, shape, dev):
+    """Generator.integers(low, high, size, int64, endpoint) in HBM, bit-identical (nb_pcg64_integers)."""
+    if high is None:
+        low, high = 0, low
+    low, high = int(low), int(high)
+    if not endpoint:
+        high -= 1
+    lo64, hi64 = -(1 << 63), (1 << 63) - 1
+    if low < lo64:
+        raise ValueError("low is out of bounds for int64")
+    if high > hi64:
+        raise ValueError("high is out of bounds for int64")
+    if low > high:
+        raise ValueError("low > high" if endpoint else "low >= high")
+    lib = _lib.load()
+    state, inc = _stream_state(rng_params)
+    out = dv.empty((size,), np.int64, dev)
+    rng = high - low
+    sc = dv.scratch(lib.nb_pcg64_integers_scratch_bytes(size, rng), dev)
+    _lib.check(lib.nb_pcg64_integers(dev, size, state, inc, low, rng, out.ptr, sc.data_ptr(), sc.numel(),
+                                     dv.stream_ptr(dev)))
+    return DeviceBlock(out.t.view(tuple(shape)))
+
+
+def _check_int_power(K, exponent):
+    # NumPy raises for integer ** negative integer; the device kernel cannot raise, so test first.
+    if exponent.size == 0:
+        return
+    lo = dv.to_numpy(K.reduce_axis("min", exponent, None, False, False))
+    if int(lo) < 0:
+        raise ValueError("Integers to negative integer powers are not allowed.")
+
+
+def _matmul(K, a1, a2):
+    # np.matmul semantics for <= 2-d operands (numpy_kernel.py:420-424)
+    dev = a1.device_index
+    lib = _lib.load()
+    if a1.ndim == 0 or a2.ndim == 0:
+        raise ValueError("matmul: Input operand does not have enough dimensions")
+    res_dtype = np.result_type(a1.dtype, a2.dtype)
+    if res_dtype == np.dtype(np.bool_):
+        raise NotImplementedError("matmul of boolean blocks")
+    want = np.dtype(np.float64) if res_dtype.kind == "f" else np.dtype(np.int64)
+    if a1.dtype != want:
+        a1 = K.astype(a1, want.name)
+    if a2.dtype != want:
+        a2 = K.astype(a2, want.name)
+    # shapes: (m,k)@(k,n), (m,k)@(k,), (k,)@(k,n), (k,)@(k,)
+    m = a1.shape[0] if a1.ndim == 2 else 1
+    k = a1.shape[-1]
+    n = a2.shape[1] if a2.ndim == 2 else 1
+    if a2.shape[0] != k:
+        raise ValueError("matmul: Input operand 1 has a mismatch in its core dimension 0 (size %d is different "
+                         "from %d)" % (a2.shape[0], k))
+    if a1.ndim == 2:
+        a_rs, a_cs = a1.strides
+    else:
+        a_rs, a_cs = 0, a1.strides[0]
+    if a2.ndim == 2:
+        b_rs, b_cs = a2.strides
+    else:
+        b_rs, b_cs = a2.strides[0], 0
+    # the kernels need one unit stride per matrix operand; make odd views contiguous
+    if a1.ndim == 2 and m > 1 and k > 1 and 1 not in (a_rs, a_cs):
+        a1 = dv.contiguous(a1)
+        a_rs, a_cs = a1.strides
+    if a2.ndim == 2 and n > 1 and k > 1 and 1 not in (b_rs, b_cs):
+        a2 = dv.contiguous(a2)
+        b_rs, b_cs = a2.strides
+    out_shape = ((m,) if a1.ndim == 2 else ()) + ((n,) if a2.ndim == 2 else ())
+    out = dv.empty(out_shape, want, dev)
+    if out.size == 0:
+        return out
+    st = dv.stream_ptr(dev)
+    if want == np.dtype(np.float64):
+        nbytes = lib.nb_matmul_scratch_bytes(dev, m, n, k)
+        sc = dv.scratch(nbytes, dev)
+        _lib.check(lib.nb_matmul_f64(dev, m, n, k, a1.ptr, a_rs, a_cs, a2.ptr, b_rs, b_cs, None, out.ptr, n,
+                                     sc.data_ptr(), sc.numel(), st))
+    else:
+        _lib.check(lib.nb_matmul_i64(dev, m, n, k, a1.ptr, a_rs, a_cs, a2.ptr, b_rs, b_cs, out.ptr, n, st))
+    return out
+
+
+def _f64_matrix(K, arr, dev):
+    src = dv.contiguous(dv.to_device(arr, dev))
+    if src.ndim != 2:
+        raise np.linalg.LinAlgError("%d-dimensional array given. Array must be two-dimensional" % src.ndim)
+    if src.dtype != np.dtype(np.float64):
+        src = K.astype(src, "float64")
+    return src
+
+
+def _concat2d(mats, axis, dev):
+    """np.concatenate of float64 matrices along `axis`, by strided device copies (nb_copy_strided)."""
+    other = mats[0].shape[1 - axis]
+    total = sum(b.shape[axis] for b in mats)
+    out = dv.empty((total, other) if axis == 0 else (other, total), np.float64, dev)
+    lo = 0
+    for b in mats:
+        if b.shape[1 - axis] != other:
+            raise ValueError("all the input array dimensions except for the concatenation axis must match exactly")
+        hi = lo + b.shape[axis]
+        dv.copy_into(out.t[lo:hi] if axis == 0 else out.t[:, lo:hi], b.t)
+        lo = hi
+    return out
+
+
+def _chol_lower(K, a, dev):
+    """Lower Cholesky factor or None when a is not positive definite (one 4-byte read-back)."""
+    lib = _lib.load()
+    p = a.shape[0]
+    out = dv.empty((p, p), np.float64, dev)
+    info = dv.empty((1,), np.int32, dev)
+    _lib.check(lib.nb_cholesky_f64(dev, p, a.ptr, out.ptr, info.ptr, dv.stream_ptr(dev)))
+    return out if int(dv.to_numpy(info)[0]) == 0 else None
+
+
+def _cholqr_pass(K, Y, dev, shift=0.0):
+    """One Cholesky-QR pass: Y = Q R with R = chol(Y^T Y + shift I)^T.  Returns (Q, R) or None."""
+    n = Y.shape[1]
+    G = K.bop("tensordot", Y, Y, True, False, 1)
+    if shift:
+        eye = dv.empty((n, n), np.float64, dev)
+        _lib.check(_lib.load().nb_eye(dev, n, n, eye.ptr, eye.code, dv.stream_ptr(dev)))
+        G = K.bop("add", G, K.bop("mul", eye, dv.from_numpy(np.float64(shift), dev), False, False, {}),
+                     False, False, {})
+    L = _chol_lower(self, G, dev)
+    if L is None:
+        return None
+    R = dv.contiguous(L.T)
+    Rinv = K.inv(R)
+    return K.bop("tensordot", Y, Rinv, False, False, 1), R, Rinv
+
 
 class KernelCls:
+
     # ---------------------------------------------------------------- I/O, creation, plumbing
     def touch(self, arr):
         # numpy_kernel.py:90 — used to wait for a computation without fetching data.
@@ -105,75 +271,26 @@ class KernelCls:
         # by the reference's own host RNG and uploaded; see DESIGN.md "inputs".
         dev = _cur(device_index)
         f64 = np.dtype(dtype) == np.dtype(np.float64)
-        if rfunc_name == "random" and len(rfunc_args) == 1 and f64:
-            return self._random_on_device(rng_params, int(rfunc_args[0]), shape, dev)
+        if rfunc_name == "random" and f64 and (len(rfunc_args) == 1 or (
+                len(rfunc_args) == 2 and np.dtype(rfunc_args[1]) == np.dtype(np.float64))):   # random.py:168
+            return _random_on_device(self, rng_params, int(rfunc_args[0]), shape, dev)
         if rfunc_name == "normal" and len(rfunc_args) == 3 and f64 and np.isscalar(rfunc_args[0]) \
                 and np.isscalar(rfunc_args[1]):
             loc, scale, size = rfunc_args
             if scale < 0:
                 raise ValueError("scale < 0")
-            return self._normal_on_device(rng_params, int(size), shape, dev, float(loc), float(scale), False)
+            return _normal_on_device(self, rng_params, int(size), shape, dev, float(loc), float(scale), False)
         if rfunc_name == "standard_normal" and len(rfunc_args) == 1 and f64:
-            return self._normal_on_device(rng_params, int(rfunc_args[0]), shape, dev, 0.0, 1.0, True)
+            return _normal_on_device(self, rng_params, int(rfunc_args[0]), shape, dev, 0.0, 1.0, True)
         if rfunc_name == "integers" and len(rfunc_args) == 5:
             low, high, size, idt, endpoint = rfunc_args
             if np.dtype(idt) == np.dtype(np.int64) and np.isscalar(low) and (high is None or np.isscalar(high)):
-                return self._integers_on_device(rng_params, low, high, int(size), bool(endpoint), shape, dev)
+                return _integers_on_device(self, rng_params, low, high, int(size), bool(endpoint), shape, dev)
         rng = block_rng(*rng_params)
         result = getattr(rng, rfunc_name)(*rfunc_args).reshape(shape)
         if rfunc_name not in ("random", "integers"):
             result = result.astype(dtype)
         return dv.from_numpy(result, dev)
-
-    @staticmethod
-    def _stream_state(rng_params):
-        """NumPy seeds and jumps the bit generator (SeedSequence + PCG64.jumped stay on the host); the device gets
-        the block's 128-bit LCG state and increment as {hi, lo} pairs."""
-        seed, jump = rng_params
-        st = PCG64(seed).jumped(jump).state["state"]
-        mask = (1 << 64) - 1
-        return ((C.c_uint64 * 2)(st["state"] >> 64, st["state"] & mask),
-                (C.c_uint64 * 2)(st["inc"] >> 64, st["inc"] & mask))
-
-    def _random_on_device(self, rng_params, size, shape, dev):
-        """Uniform doubles generated in HBM, bit-identical to the host stream (nb_pcg64_random)."""
-        state, inc = self._stream_state(rng_params)
-        out = dv.empty((size,), np.float64, dev)
-        _lib.check(_lib.load().nb_pcg64_random(dev, size, state, inc, out.ptr, dv.stream_ptr(dev)))
-        return DeviceBlock(out.t.view(tuple(shape)))
-
-    def _normal_on_device(self, rng_params, size, shape, dev, loc, scale, standard):
-        """Generator.normal / standard_normal in HBM, in the host generator's order (nb_pcg64_normal)."""
-        lib = _lib.load()
-        state, inc = self._stream_state(rng_params)
-        out = dv.empty((size,), np.float64, dev)
-        sc = dv.scratch(lib.nb_pcg64_normal_scratch_bytes(size), dev)
-        _lib.check(lib.nb_pcg64_normal(dev, size, state, inc, loc, scale, 1 if standard else 0, out.ptr,
-                                       sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
-        return DeviceBlock(out.t.view(tuple(shape)))
-
-    def _integers_on_device(self, rng_params, low, high, size, endpoint, shape, dev):
-        """Generator.integers(low, high, size, int64, endpoint) in HBM, bit-identical (nb_pcg64_integers)."""
-        if high is None:
-            low, high = 0, low
-        low, high = int(low), int(high)
-        if not endpoint:
-            high -= 1
-        lo64, hi64 = -(1 << 63), (1 << 63) - 1
-        if low < lo64:
-            raise ValueError("low is out of bounds for int64")
-        if high > hi64:
-            raise ValueError("high is out of bounds for int64")
-        if low > high:
-            raise ValueError("low > high" if endpoint else "low >= high")
-        lib = _lib.load()
-        state, inc = self._stream_state(rng_params)
-        out = dv.empty((size,), np.int64, dev)
-        rng = high - low
-        sc = dv.scratch(lib.nb_pcg64_integers_scratch_bytes(size, rng), dev)
-        _lib.check(lib.nb_pcg64_integers(dev, size, state, inc, low, rng, out.ptr, sc.data_ptr(), sc.numel(),
-                                         dv.stream_ptr(dev)))
-        return DeviceBlock(out.t.view(tuple(shape)))
 
     def permutation(self, rng_params, size, device_index=None):
         # numpy_kernel.py:112-114, generated in HBM (csrc/perm.cu), bit-identical to the host generator's shuffle
@@ -182,7 +299,7 @@ class KernelCls:
         if size >= 2 ** 31:
             return dv.from_numpy(block_rng(*rng_params).permutation(size), dev)
         lib = _lib.load()
-        state, inc = self._stream_state(rng_params)
+        state, inc = _stream_state(rng_params)
         out = dv.empty((size,), np.int64, dev)
         if size == 0:
             return out
@@ -286,7 +403,12 @@ class KernelCls:
 
     def astype(self, arr, dtype_str):
         # numpy_kernel.py:339-341
-        dtype = np.dtype(getattr(np, dtype_str)) if isinstance(dtype_str, str) else np.dtype(dtype_str)
+        if isinstance(dtype_str, str):
+            # the reference does getattr(np, dtype_str) with names such as "int" (glms.py:508, NumPy < 1.24 aliases)
+            dtype_str = {"int": "int64", "float": "float64", "bool": "bool_"}.get(dtype_str, dtype_str)
+            dtype = np.dtype(getattr(np, dtype_str))
+        else:
+            dtype = np.dtype(dtype_str)
         dev = arr.device_index
         src = dv.contiguous(arr)
         out = dv.empty(src.shape, dtype, dev)
@@ -305,11 +427,11 @@ class KernelCls:
             a2 = a2.T
         if op == "tensordot":
             if axes == 1 and max(a1.ndim, a2.ndim) <= 2:
-                return self._matmul(a1, a2)
+                return _matmul(self, a1, a2)
             raise NotImplementedError("tensordot with axes=%s on %d-d/%d-d blocks" % (axes, a1.ndim, a2.ndim))
         code, cdt, odt = hl.resolve_bop(op, a1.dtype, a2.dtype)
         if hl.canonical_bop(op) == "power" and cdt == hl.NB_I64:
-            self._check_int_power(a2)
+            _check_int_power(self, a2)
         shape, sa, sb = hl.broadcast_geometry(a1.shape, a1.strides, a2.shape, a2.strides)
         cshape, csa, csb = hl.collapse_dims(shape, sa, sb)
         if len(cshape) > 4:
@@ -323,64 +445,6 @@ class KernelCls:
             _lib.check(_lib.load().nb_bop(
                 dev, code, len(cshape), _lib.i64_array(cshape), a1.ptr, a1.code, _lib.i64_array(csa),
                 a2.ptr, a2.code, _lib.i64_array(csb), out.ptr, out.code, cdt, dv.stream_ptr(dev)))
-        return out
-
-    def _check_int_power(self, exponent):
-        # NumPy raises for integer ** negative integer; the device kernel cannot raise, so test first.
-        if exponent.size == 0:
-            return
-        lo = dv.to_numpy(self.reduce_axis("min", exponent, None, False, False))
-        if int(lo) < 0:
-            raise ValueError("Integers to negative integer powers are not allowed.")
-
-    def _matmul(self, a1, a2):
-        # np.matmul semantics for <= 2-d operands (numpy_kernel.py:420-424)
-        dev = a1.device_index
-        lib = _lib.load()
-        if a1.ndim == 0 or a2.ndim == 0:
-            raise ValueError("matmul: Input operand does not have enough dimensions")
-        res_dtype = np.result_type(a1.dtype, a2.dtype)
-        if res_dtype == np.dtype(np.bool_):
-            raise NotImplementedError("matmul of boolean blocks")
-        want = np.dtype(np.float64) if res_dtype.kind == "f" else np.dtype(np.int64)
-        if a1.dtype != want:
-            a1 = self.astype(a1, want.name)
-        if a2.dtype != want:
-            a2 = self.astype(a2, want.name)
-        # shapes: (m,k)@(k,n), (m,k)@(k,), (k,)@(k,n), (k,)@(k,)
-        m = a1.shape[0] if a1.ndim == 2 else 1
-        k = a1.shape[-1]
-        n = a2.shape[1] if a2.ndim == 2 else 1
-        if a2.shape[0] != k:
-            raise ValueError("matmul: Input operand 1 has a mismatch in its core dimension 0 (size %d is different "
-                             "from %d)" % (a2.shape[0], k))
-        if a1.ndim == 2:
-            a_rs, a_cs = a1.strides
-        else:
-            a_rs, a_cs = 0, a1.strides[0]
-        if a2.ndim == 2:
-            b_rs, b_cs = a2.strides
-        else:
-            b_rs, b_cs = a2.strides[0], 0
-        # the kernels need one unit stride per matrix operand; make odd views contiguous
-        if a1.ndim == 2 and m > 1 and k > 1 and 1 not in (a_rs, a_cs):
-            a1 = dv.contiguous(a1)
-            a_rs, a_cs = a1.strides
-        if a2.ndim == 2 and n > 1 and k > 1 and 1 not in (b_rs, b_cs):
-            a2 = dv.contiguous(a2)
-            b_rs, b_cs = a2.strides
-        out_shape = ((m,) if a1.ndim == 2 else ()) + ((n,) if a2.ndim == 2 else ())
-        out = dv.empty(out_shape, want, dev)
-        if out.size == 0:
-            return out
-        st = dv.stream_ptr(dev)
-        if want == np.dtype(np.float64):
-            nbytes = lib.nb_matmul_scratch_bytes(dev, m, n, k)
-            sc = dv.scratch(nbytes, dev)
-            _lib.check(lib.nb_matmul_f64(dev, m, n, k, a1.ptr, a_rs, a_cs, a2.ptr, b_rs, b_cs, None, out.ptr, n,
-                                         sc.data_ptr(), sc.numel(), st))
-        else:
-            _lib.check(lib.nb_matmul_i64(dev, m, n, k, a1.ptr, a_rs, a_cs, a2.ptr, b_rs, b_cs, out.ptr, n, st))
         return out
 
     def bop_reduce(self, op, a1, a2, a1_T, a2_T):
@@ -569,39 +633,6 @@ class KernelCls:
         return out
 
     # ---------------------------------------------------------------- factorisations
-    def _f64_matrix(self, arr, dev):
-        src = dv.contiguous(dv.to_device(arr, dev))
-        if src.ndim != 2:
-            raise np.linalg.LinAlgError("%d-dimensional array given. Array must be two-dimensional" % src.ndim)
-        if src.dtype != np.dtype(np.float64):
-            src = self.astype(src, "float64")
-        return src
-
-    def _chol_lower(self, a, dev):
-        """Lower Cholesky factor or None when a is not positive definite (one 4-byte read-back)."""
-        lib = _lib.load()
-        p = a.shape[0]
-        out = dv.empty((p, p), np.float64, dev)
-        info = dv.empty((1,), np.int32, dev)
-        _lib.check(lib.nb_cholesky_f64(dev, p, a.ptr, out.ptr, info.ptr, dv.stream_ptr(dev)))
-        return out if int(dv.to_numpy(info)[0]) == 0 else None
-
-    def _cholqr_pass(self, Y, dev, shift=0.0):
-        """One Cholesky-QR pass: Y = Q R with R = chol(Y^T Y + shift I)^T.  Returns (Q, R) or None."""
-        n = Y.shape[1]
-        G = self.bop("tensordot", Y, Y, True, False, 1)
-        if shift:
-            eye = dv.empty((n, n), np.float64, dev)
-            _lib.check(_lib.load().nb_eye(dev, n, n, eye.ptr, eye.code, dv.stream_ptr(dev)))
-            G = self.bop("add", G, self.bop("mul", eye, dv.from_numpy(np.float64(shift), dev), False, False, {}),
-                         False, False, {})
-        L = self._chol_lower(G, dev)
-        if L is None:
-            return None
-        R = dv.contiguous(L.T)
-        Rinv = self.inv(R)
-        return self.bop("tensordot", Y, Rinv, False, False, 1), R, Rinv
-
     def qr(self, *arrays, mode="reduced", axis=None):
         """numpy_kernel.py:455-461: np.linalg.qr of the concatenated operands, modes "r" and "reduced".
 
@@ -616,34 +647,31 @@ class KernelCls:
         in_dtype = arrays[0].dtype
         if len(arrays) > 1:
             assert axis is not None
-            mats = [self._f64_matrix(a, dev) for a in arrays]
-            import torch
-            X = DeviceBlock(torch.cat([b.t for b in mats], dim=axis))
+            X = _concat2d([_f64_matrix(self, a, dev) for a in arrays], axis, dev)
         else:
-            X = self._f64_matrix(arrays[0], dev)
+            X = _f64_matrix(self, arrays[0], dev)
         m, n = X.shape
         back = (lambda b: b) if in_dtype == np.dtype(np.float64) else (lambda b: self.astype(b, in_dtype.name))
         if m < n:
             # wide block (a column-blocked covariance in linalg.pca): LAPACK reflects the leading m x m part and
             # carries the other columns along, R = [R1, Q^T A2]
-            import torch
             Q, R1 = self.qr(dv.contiguous(DeviceBlock(X.t[:, :m])), mode="reduced")
             R2 = self.bop("tensordot", Q, dv.contiguous(DeviceBlock(X.t[:, m:])), True, False, 1)
-            R = DeviceBlock(torch.cat([R1.t, R2.t], dim=1))
+            R = _concat2d([R1, R2], 1, dev)
             return back(R) if mode == "r" else (back(Q), back(R))
         lib = _lib.load()
         st = dv.stream_ptr(dev)
-        first = self._cholqr_pass(X, dev)
+        first = _cholqr_pass(self, X, dev)
         passes = []
         if first is None:
             # shifted CholeskyQR3: the shift makes the first Gram matrix safely positive definite
             fro2 = float(dv.to_numpy(self.bop("tensordot", DeviceBlock(X.t.reshape(-1)),
                                              DeviceBlock(X.t.reshape(-1)), False, False, 1)))
             shift = 11.0 * (m * n + n * (n + 1)) * np.finfo(np.float64).eps * fro2
-            first = self._cholqr_pass(X, dev, shift)
+            first = _cholqr_pass(self, X, dev, shift)
             if first is None:
                 raise np.linalg.LinAlgError("qr: block is numerically rank deficient beyond the shifted Cholesky QR")
-            second = self._cholqr_pass(first[0], dev)
+            second = _cholqr_pass(self, first[0], dev)
             if second is None:
                 raise np.linalg.LinAlgError("qr: block is numerically rank deficient beyond the shifted Cholesky QR")
             passes = [first, second]
@@ -653,7 +681,7 @@ class KernelCls:
             Y = first[0]
         # last pass: keep R^-1 apart so that mode "r" never forms the final Q
         G = self.bop("tensordot", Y, Y, True, False, 1)
-        L = self._chol_lower(G, dev)
+        L = _chol_lower(self, G, dev)
         if L is None:
             raise np.linalg.LinAlgError("qr: Gram matrix of the orthogonalised block is not positive definite")
         R = dv.contiguous(L.T)
@@ -676,10 +704,10 @@ class KernelCls:
     def cholesky(self, arr):
         # numpy_kernel.py:463-464
         dev = arr.device_index
-        a = self._f64_matrix(arr, dev)
+        a = _f64_matrix(self, arr, dev)
         if a.shape[0] != a.shape[1]:
             raise np.linalg.LinAlgError("Last 2 dimensions of the array must be square")
-        L = self._chol_lower(a, dev)
+        L = _chol_lower(self, a, dev)
         if L is None:
             raise np.linalg.LinAlgError("Matrix is not positive definite")
         return L if arr.dtype == np.dtype(np.float64) else self.astype(L, arr.dtype.name)
@@ -687,7 +715,7 @@ class KernelCls:
     def svd(self, arr):
         # numpy_kernel.py:466-469 for the square R of a tall-skinny factorisation (linalg.py:221-223)
         dev = arr.device_index
-        a = self._f64_matrix(arr, dev)
+        a = _f64_matrix(self, arr, dev)
         p = a.shape[0]
         if a.shape[1] != p:
             raise NotImplementedError("svd of a non-square block (%d x %d)" % a.shape)

@@ -210,3 +210,20 @@ def test_parallel_permutation_formulation_equals_numpy():
         for jump in (0, 5):
             got, _, rounds, _ = pp.permutation(n, 99, jump)
             assert np.array_equal(got, Generator(PCG64(99).jumped(jump)).permutation(n)), (n, jump)
+
+
+def test_reference_layers_drive_the_plugin_host_logic():
+    """The unmodified reference (oracle/_ref) registers cuda_kernel in its own KernelManager and drives
+    CudaBackend / KernelCls through whole programs; the library's compute calls are stubbed
+    (tools/dryrun_reference_boundary.py), so only the host logic is exercised.  The values are checked on the GPU by
+    tests/test_gpu_reference_boundary.py."""
+    import subprocess
+    import sys
+    from oracle import refharness
+    if not refharness.present():
+        pytest.skip("oracle/_ref absent (python oracle/make_ref.py)")
+    for gpus in ("1", "2"):
+        proc = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "dryrun_reference_boundary.py"), gpus],
+                              capture_output=True, text=True, timeout=600)
+        assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+        assert proc.stdout.count("\nok") + proc.stdout.startswith("ok") >= 14
