@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdarg.h>
 #include <math.h>
+#include <stdlib.h>
 #include "../../include/nums_b200.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
@@ -37,6 +38,33 @@ const DevInfo& dev_info(int device);
   } while (0)
 
 #define NB_LAUNCH_CHECK() NB_CHECK(cudaGetLastError())
+
+// A debug switch read from the environment once per process.
+#define NB_ENV_FLAG(name) ([]() -> bool { static const bool v = getenv(name) != nullptr; return v; }())
+
+// Launch set-up that belongs to (kernel, device), not to every call: the dynamic shared memory opt-in and the
+// occupancy query cost microseconds each and sit in the per-iteration launch path of the GLM kernels.  One static
+// instance per call site (i.e. per kernel instantiation).
+constexpr int NB_MAX_DEVICES = 16;
+struct KernelSetup {
+  bool done[NB_MAX_DEVICES] = {};
+  int occ[NB_MAX_DEVICES] = {};
+  template <typename K>
+  int get(int device, K kern, int threads, size_t smem, int* out_occ) {
+    const bool cached = device >= 0 && device < NB_MAX_DEVICES && done[device];
+    if (!cached) {
+      NB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int o = 1;
+      NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, threads, smem));
+      if (o < 1) o = 1;
+      if (device >= 0 && device < NB_MAX_DEVICES) { occ[device] = o; done[device] = true; }
+      *out_occ = o;
+      return 0;
+    }
+    *out_occ = occ[device];
+    return 0;
+  }
+};
 
 static inline int item_size(int dt) {
   switch (dt) {

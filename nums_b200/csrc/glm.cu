@@ -386,31 +386,8 @@ int glm_regs_pass1(int device, int family, const double* x, int64_t n, int64_t d
                    cudaStream_t st);
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
-int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
-                    int ydt, const double* beta, const double* wext, bool link, double* stats, int64_t ldc,
-                    void* scratch, size_t scratch_bytes, cudaStream_t st);
-// glm_rows_tma.cu
-bool rows_tma_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
-int glm_rows_tma(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
-                 const double* beta, int want_hess, double* wbuf, double* partials, int max_parts, int* nparts,
-                 cudaStream_t st);
-static int rows_mode() {     // 0 (default): register-resident k_glm_rows; 1: TMA-staged variant (experimental, slower)
-  static int mode = -1;
-  if (mode < 0) {
-    const char* e = getenv("NUMS_B200_ROWS_MODE");
-    mode = e ? atoi(e) : 0;
-  }
-  return mode;
-}
-// 0: two passes, pass 2 = triangular DMMA kernel (default); 1: single fused pass; 2: two passes, pass 2 = generic GEMM
-static int glm_mode() {
-  static int mode = -1;
-  if (mode < 0) {
-    const char* e = getenv("NUMS_B200_GLM_MODE");
-    mode = e ? atoi(e) : 0;
-  }
-  return mode;
-}
+int tri_gram(int device, const double* x, int64_t n, int64_t d, int64_t ldx, const double* wext, double* out,
+             int64_t ldc, void* scratch, size_t scratch_bytes, cudaStream_t st);
 
 struct GlmLayout {
   size_t off_w, off_parts, off_gemm, total;
@@ -434,7 +411,7 @@ static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
   cur += align256(parts_bytes);
   L.off_gemm = cur;
   if (want_hess && d >= 8) cur += align256(gemm_scratch_bytes(device, d, d, n));
-  if (want_hess && d >= 8 && d <= 256) {   // the triangular / single-pass kernels take their partials from the GEMM region
+  if (want_hess && d >= 8 && d <= 256) {   // the triangular kernel takes their partials from the GEMM region
     size_t f = L.off_gemm + align256(fused_scratch_bytes(device, n, d));
     if (f > cur) cur = f;
   }
@@ -477,10 +454,9 @@ template <int NJ, int WPR, bool VEC, bool HESS>
 static int launch_rows_h(int device, const GlmRowsArgs& a, int max_parts, int* nparts, cudaStream_t st) {
   auto kern = k_glm_rows<NJ, WPR, VEC, HESS>;
   size_t smem = (3 * (size_t)WPR * 64 * NJ + 4) * sizeof(double);
-  NB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static KernelSetup setup;          // the shared-memory size depends on the template arguments only
   int occ = 1;
-  NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, GLM_THREADS, smem));
-  if (occ < 1) occ = 1;
+  if (int rc = setup.get(device, kern, GLM_THREADS, smem, &occ)) return rc;
   constexpr int R = RowsCfg<NJ, HESS>::R;
   constexpr int RG = (GLM_THREADS / 32) / WPR;
   int64_t batches = (a.n + R - 1) / R;
@@ -554,9 +530,6 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   if (glm_regs_applicable(d, want_hess))
     return glm_regs_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, skip_obj, stats_d, sc, L.total, st);
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);
-  if (tri_ok && glm_mode() == 1)
-    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, nullptr, true, stats_d, d + 1,
-                           sc + L.off_gemm, L.total - L.off_gemm, st);
   GlmRowsArgs a;
   a.x = x_d; a.n = n; a.d = d; a.ldx = ldx; a.y = y_d; a.ydt = ydt; a.beta = beta_d;
   a.family = family; a.want_hess = want_hess; a.skip_obj = skip_obj;
@@ -566,26 +539,21 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   int nparts = 0;
   const bool vec = ((ldx & 1) == 0) && ((((uintptr_t)x_d) & 15) == 0);
   int rc;
-  if (tri_ok && glm_mode() == 0 && glm_regs_pass1_applicable(d)) {
+  if (tri_ok && glm_regs_pass1_applicable(d)) {
     // 64 < d <= 192: the register-resident kernel is the faster first pass (its partials live in the parts region)
     rc = glm_regs_pass1(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, skip_obj, a.wbuf, stats_d, parts,
                         L.off_gemm - L.off_parts, st);
     if (rc) return rc;
-    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, false, stats_d, d + 1,
-                           sc + L.off_gemm, L.total - L.off_gemm, st);
+    return tri_gram(device, x_d, n, d, ldx, a.wbuf, stats_d, d + 1, sc + L.off_gemm, L.total - L.off_gemm, st);
   }
-  if (rows_mode() == 1 && rows_tma_applicable(n, d, ldx, x_d))
-    rc = glm_rows_tma(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, a.wbuf, parts, L.max_parts, &nparts, st);
-  else
-    rc = vec ? launch_rows_cfg<true>(device, a, L.max_parts, &nparts, st)
-             : launch_rows_cfg<false>(device, a, L.max_parts, &nparts, st);
+  rc = vec ? launch_rows_cfg<true>(device, a, L.max_parts, &nparts, st)
+           : launch_rows_cfg<false>(device, a, L.max_parts, &nparts, st);
   if (rc) return rc;
   k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, nparts, parts, want_hess, stats_d);
   NB_LAUNCH_CHECK();
-  if (tri_ok && glm_mode() == 0) {
+  if (tri_ok) {
     // pass 2: upper-triangular blocks of X^T diag(w) X by FP64 DMMA, mirrored -> exactly symmetric
-    return glm_fused_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, a.wbuf, false, stats_d, d + 1,
-                           sc + L.off_gemm, L.total - L.off_gemm, st);
+    return tri_gram(device, x_d, n, d, ldx, a.wbuf, stats_d, d + 1, sc + L.off_gemm, L.total - L.off_gemm, st);
   }
   if (want_hess) {
     // G = X^T diag(w) X into the top-left d x d of the p x p Hessian (row stride p)

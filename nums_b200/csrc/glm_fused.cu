@@ -1,5 +1,5 @@
-// Newton statistics for 8 <= d <= 256 (nums/models/glms.py:457-499 as called from newton() :660-676) on
-// the FP64 tensor pipe, warp-specialised.
+// The Hessian X^T diag(w) X for 8 <= d <= 256 (nums/models/glms.py:491-499 as called from newton() :660-676; also
+// the plain symmetric Gram X^T X) on the FP64 tensor pipe, warp-specialised.
 //
 // A group of C CTAs walks one contiguous range of rows, 16 rows per pipeline stage.  Rows are staged whole
 // (all d columns, padded stride = 4 mod 16 doubles -> conflict-free DMMA fragment loads) so that every
@@ -10,14 +10,10 @@
 // Roles inside a CTA (no block-wide barrier in steady state, only mbarriers per stage slot):
 //   producer warp   lane r issues the TMA bulk copy (cp.async.bulk, SASS UBLKCP) of row r of the stage and
 //                   arrives on the slot's "fullx" barrier with its own byte count;
-//   consumer warps  wait fullx (+ fullw), accumulate their block with DMMA.8x8x4 (A fragments scaled by w),
-//                   arrive on "empty";
-//   aux warps       (single-pass mode only) 4 warps, stage kt belongs to aux warp kt % 4: eta = x.beta from
-//                   shared memory, link -> weights w and residuals r for the 16 rows (lanes), "fullw" arrive,
-//                   then g += X^T r and u += X^T w for the stages this CTA owns (kt % C == c), "empty" arrive.
-//                   Four warps give every link evaluation four stage-times, so its exp/div chain never
-//                   holds the tensor pipe up.
-// Two-pass mode (default): weights come from pass 1 (k_glm_rows); the producer lanes store them.
+//   consumer warps  wait fullx, accumulate their block with DMMA.8x8x4 (A fragments scaled by w), arrive on "empty".
+// The weights come from the first pass (k_glm_rows / k_glm_regs); the producer lanes store them next to the rows.
+// (A single-pass variant that evaluated the link in extra warps of this kernel was measured at 48 ms against 33 ms
+// for two passes -- scalar FP64 and DMMA share one pipe -- and was removed; see DESIGN.md.)
 // Partials go to scratch per group and are summed in a fixed order by k_fused_finish; the lower triangle is
 // the mirror image of the upper one, so H is exactly symmetric.
 #include "glm_common.cuh"
@@ -61,11 +57,7 @@ __device__ __forceinline__ void fence_async_proxy() { asm volatile("fence.proxy.
 
 struct FusedArgs {
   const double* x; int64_t n, d, ldx;
-  const void* y; int ydt;
-  const double* beta;
-  const double* wext;      // two-pass mode: precomputed weights (null = all ones)
-  int family;
-  int skip_obj;            // single-pass mode: leave the objective out (Newton does not use it)
+  const double* wext;      // precomputed weights (null = all ones)
   int nblk;                // ceil(d / 32)
   int T;                   // nblk (nblk + 1) / 2 upper-triangular blocks
   int C;                   // CTAs per group
@@ -74,20 +66,17 @@ struct FusedArgs {
   int64_t rows_per_group;  // multiple of FK
   int64_t ldc;             // row stride of the output matrix (d + 1 inside the packed stats buffer)
   double* part_h;          // [groups * KG][T][32*32]
-  double* part_v;          // [groups * C][2*dp + 3]   g[dp] | u[dp] | sum r | sum w | objective
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
 
-constexpr int NAUX = 4;
-
-template <int W, int S, bool LINK>
-__global__ void __launch_bounds__((W + 1 + (LINK ? NAUX : 0)) * 32)
+template <int W, int S>
+__global__ void __launch_bounds__((W + 1) * 32)
 k_tri_gram(const FusedArgs a) {
-  constexpr int NT = (W + 1 + (LINK ? NAUX : 0)) * 32;
-  constexpr int PRODUCER = W + (LINK ? NAUX : 0);
+  constexpr int NT = (W + 1) * 32;
+  constexpr int PRODUCER = W;
   extern __shared__ __align__(16) double fsm[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int lq = lane >> 2, lr = lane & 3;
@@ -101,17 +90,14 @@ k_tri_gram(const FusedArgs a) {
 
   double* sX = fsm;                               // S * FK * ld
   double* sWgt = sX + (size_t)S * FK * ld;        // S * FK
-  double* sAux = sWgt + S * FK;                   // NAUX * (2*dp + 4): final reduction of the aux warps
-  uint64_t* fullx = reinterpret_cast<uint64_t*>(sAux + NAUX * (2 * dp + 4));
-  uint64_t* fullw = fullx + S;
-  uint64_t* empty = fullw + S;
+  uint64_t* fullx = reinterpret_cast<uint64_t*>(sWgt + S * FK);
+  uint64_t* empty = fullx + S;
 
   for (int i = tid; i < S * FK * ld; i += NT) sX[i] = 0.0;     // stale rows must be finite (their weight is 0)
   if (tid == 0) {
     for (int s = 0; s < S; s++) {
       mbar_init(&fullx[s], FK);
-      mbar_init(&fullw[s], FK);
-      mbar_init(&empty[s], W + (LINK ? 1 : 0));
+      mbar_init(&empty[s], W);
     }
   }
   fence_async_proxy();
@@ -126,91 +112,14 @@ k_tri_gram(const FusedArgs a) {
       if (lane < FK) {
         const int64_t gr = row_beg + (int64_t)kt * FK + lane;
         if (gr < row_end) {
-          if constexpr (!LINK) sWgt[slot * FK + lane] = a.wext ? a.wext[gr] : 1.0;
+          sWgt[slot * FK + lane] = a.wext ? a.wext[gr] : 1.0;
           mbar_expect_tx(&fullx[slot], row_bytes);             // this lane's arrival + its bytes
           bulk_g2s(sX + (size_t)slot * FK * ld + lane * ld, a.x + gr * a.ldx, row_bytes, &fullx[slot]);
         } else {
-          if constexpr (!LINK) sWgt[slot * FK + lane] = 0.0;
+          sWgt[slot * FK + lane] = 0.0;
           mbar_arrive(&fullx[slot]);
         }
       }
-    }
-    return;
-  }
-
-  if (LINK && warp >= W) {
-    // ---------------------------------------------------------------- aux warps (single-pass mode)
-    const int aw = warp - W;
-    double bet[8], g[8], u[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-      int col = lane + 32 * j;
-      bet[j] = (j < a.nblk && col < d) ? a.beta[col] : 0.0;
-      g[j] = 0.0; u[j] = 0.0;
-    }
-    const double beta0 = a.beta[d];
-    double acc_obj = 0.0, acc_r = 0.0, acc_w = 0.0;
-    for (int kt = aw; kt < ktiles; kt += NAUX) {
-      const int slot = kt % S;
-      mbar_wait(&fullx[slot], (unsigned)((kt / S) & 1));
-      const double* xs = sX + (size_t)slot * FK * ld;
-      double eta = 0.0;
-#pragma unroll 4
-      for (int r = 0; r < FK; r++) {
-        double s = 0.0;
-#pragma unroll
-        for (int j = 0; j < 8; j++)
-          if (j < a.nblk) s = fma(xs[r * ld + lane + 32 * j], bet[j], s);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == r) eta = s + beta0;
-      }
-      LinkOut lo;
-      lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0;
-      const int64_t gr = row_beg + (int64_t)kt * FK + lane;
-      if (lane < FK && gr < row_end)
-        lo = a.skip_obj ? glm_link_noobj_rt(a.family, eta, load_y(a.y, a.ydt, gr)) : glm_link_rt(a.family, eta, load_y(a.y, a.ydt, gr));
-      if (lane < FK) {
-        sWgt[slot * FK + lane] = lo.wgt;
-        mbar_arrive(&fullw[slot]);                 // release: the consumers may read this stage's weights
-      }
-      if ((kt % a.C) == c) {                       // this CTA owns the vector statistics of the stage
-        acc_obj += lo.obj; acc_r += lo.resid; acc_w += lo.wgt;
-#pragma unroll 4
-        for (int r = 0; r < FK; r++) {
-          const double rr = __shfl_sync(0xffffffffu, lo.resid, r);
-          const double ww = __shfl_sync(0xffffffffu, lo.wgt, r);
-#pragma unroll
-          for (int j = 0; j < 8; j++)
-            if (j < a.nblk) {
-              const double xv = xs[r * ld + lane + 32 * j];
-              g[j] = fma(rr, xv, g[j]);
-              u[j] = fma(ww, xv, u[j]);
-            }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[slot]);
-    }
-    // reduce the four aux warps in warp order and publish this CTA's partial vector
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      acc_obj += __shfl_down_sync(0xffffffffu, acc_obj, o);
-      acc_r += __shfl_down_sync(0xffffffffu, acc_r, o);
-      acc_w += __shfl_down_sync(0xffffffffu, acc_w, o);
-    }
-    double* mine = sAux + aw * (2 * dp + 4);
-#pragma unroll
-    for (int j = 0; j < 8; j++)
-      if (j < a.nblk) { mine[lane + 32 * j] = g[j]; mine[dp + lane + 32 * j] = u[j]; }
-    if (lane == 0) { mine[2 * dp] = acc_r; mine[2 * dp + 1] = acc_w; mine[2 * dp + 2] = acc_obj; }
-    asm volatile("bar.sync 1, %0;" :: "n"(NAUX * 32));
-    double* pv = a.part_v + ((size_t)group * a.C + c) * (2 * dp + 3);
-    for (int i = (warp - W) * 32 + lane; i < 2 * dp + 3; i += NAUX * 32) {
-      double s = 0.0;
-#pragma unroll
-      for (int q = 0; q < NAUX; q++) s += sAux[q * (2 * dp + 4) + i];
-      pv[i] = s;
     }
     return;
   }
@@ -245,7 +154,6 @@ k_tri_gram(const FusedArgs a) {
     // every consumer waits (also a warp without a block): it keeps a fast warp from arriving twice on
     // the same "empty" phase
     mbar_wait(&fullx[slot], (unsigned)((kt / S) & 1));
-    if constexpr (LINK) mbar_wait(&fullw[slot], (unsigned)((kt / S) & 1));
     if (has_block && a.KG == 1) {
       const double* xs = sX + (size_t)slot * FK * ld;
       const double* ws = sWgt + slot * FK;
@@ -301,45 +209,28 @@ k_tri_gram(const FusedArgs a) {
   }
 }
 
-// Sums the group partials in group order and assembles the packed [H | g | obj] buffer.
+// Sums the group partials in group order into the upper triangle of the d x d corner of `out` and mirrors it.
 __global__ void __launch_bounds__(256)
-k_fused_finish(const FusedArgs a, double* __restrict__ stats, int h_only) {
+k_fused_finish(const FusedArgs a, double* __restrict__ out) {
   const int64_t d = a.d, p = a.ldc;
-  const int dp = a.nblk * FB;
   const int64_t nh = d * (d + 1) / 2;                // upper triangle of the d x d part
-  const int64_t total = h_only ? nh : nh + 2 * d + 3;
-  for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < total; e += (int64_t)gridDim.x * 256) {
-    if (e < nh) {
-      // e -> (i, j), i <= j, row by row
-      int64_t i = 0, rem = e;
-      // closed form would need a sqrt; d <= 256 so a short search is fine
-      while (rem >= d - i) { rem -= d - i; i++; }
-      int64_t j = i + rem;
-      int bi = (int)(i / FB), bj = (int)(j / FB);
-      int t = bi * a.nblk - (bi * (bi - 1)) / 2 + (bj - bi);
-      const double* src = a.part_h + (size_t)t * (FB * FB) + (i - bi * FB) * FB + (j - bj * FB);
-      const double s = sum_partials(src, (size_t)a.T * (FB * FB), a.groups * a.KG);
-      stats[i * p + j] = s;
-      stats[j * p + i] = s;
-    } else {
-      int64_t q = e - nh;
-      int64_t idx;                                   // index into the per-group vector
-      if (q < d) idx = q;                            // g[q]
-      else if (q < 2 * d) idx = dp + (q - d);        // u[q - d]
-      else idx = 2 * dp + (q - 2 * d);               // sum r, sum w, objective
-      const double s = sum_partials(a.part_v + idx, (size_t)(2 * dp + 3), a.groups * a.C);
-      if (q < d) stats[p * p + q] = s;
-      else if (q < 2 * d) { int64_t i = q - d; stats[i * p + d] = s; stats[d * p + i] = s; }
-      else if (q == 2 * d) stats[p * p + d] = s;
-      else if (q == 2 * d + 1) stats[d * p + d] = s;
-      else stats[p * p + p] = s;
-    }
+  for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < nh; e += (int64_t)gridDim.x * 256) {
+    // e -> (i, j), i <= j, row by row (a closed form would need a sqrt; d <= 256 so a short search is fine)
+    int64_t i = 0, rem = e;
+    while (rem >= d - i) { rem -= d - i; i++; }
+    int64_t j = i + rem;
+    int bi = (int)(i / FB), bj = (int)(j / FB);
+    int t = bi * a.nblk - (bi * (bi - 1)) / 2 + (bj - bi);
+    const double* src = a.part_h + (size_t)t * (FB * FB) + (i - bi * FB) * FB + (j - bj * FB);
+    const double s = sum_partials(src, (size_t)a.T * (FB * FB), a.groups * a.KG);
+    out[i * p + j] = s;
+    out[j * p + i] = s;
   }
 }
 
-struct FusedPlan { int W, S, nblk, T, C, KG, groups; int64_t rows_per_group; size_t smem, scratch, off_v; };
+struct FusedPlan { int W, S, nblk, T, C, KG, groups; int64_t rows_per_group; size_t smem, scratch; };
 
-static FusedPlan plan_fused(int device, int64_t n, int64_t d, bool link) {
+static FusedPlan plan_fused(int device, int64_t n, int64_t d) {
   FusedPlan f;
   f.nblk = (int)((d + FB - 1) / FB);
   f.T = f.nblk * (f.nblk + 1) / 2;
@@ -359,13 +250,11 @@ static FusedPlan plan_fused(int device, int64_t n, int64_t d, bool link) {
   if (f.groups < 1) f.groups = 1;
   const int dp = f.nblk * FB, ld = dp + FPAD;
   const size_t stage = (size_t)FK * ld * sizeof(double);
-  const size_t fixed = (size_t)NAUX * (2 * dp + 4) * 8 + 3 * 8 * 8 + 64;
-  f.S = link ? 6 : 5;                               // single-pass mode keeps three stages with the aux warps
+  const size_t fixed = 2 * 8 * 8 + 64;
+  f.S = 5;
   while (f.S > 4 && (size_t)f.S * (stage + FK * 8) + fixed > (size_t)220 * 1024) f.S--;
   f.smem = (size_t)f.S * (stage + FK * 8) + fixed;
-  size_t ph = (size_t)f.groups * f.KG * f.T * FB * FB * sizeof(double);
-  f.off_v = (ph + 255) & ~(size_t)255;
-  f.scratch = f.off_v + (((size_t)f.groups * f.C * (2 * dp + 3) * sizeof(double) + 255) & ~(size_t)255);
+  f.scratch = ((size_t)f.groups * f.KG * f.T * FB * FB * sizeof(double) + 255) & ~(size_t)255;
   return f;
 }
 
@@ -375,62 +264,45 @@ bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x) {
 }
 
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d) {
-  // upper bound over n (the group count only shrinks for tiny n) and over both modes
-  size_t best = 0;
-  for (int link = 0; link < 2; link++) {
-    FusedPlan f = plan_fused(device, n > 0 ? n : 1, d, link != 0);
-    FusedPlan g = plan_fused(device, (int64_t)1 << 40, d, link != 0);
-    if (f.scratch > best) best = f.scratch;
-    if (g.scratch > best) best = g.scratch;
-  }
-  return best;
+  // upper bound over n (the group count only shrinks for tiny n)
+  const FusedPlan f = plan_fused(device, n > 0 ? n : 1, d);
+  const FusedPlan g = plan_fused(device, (int64_t)1 << 40, d);
+  return f.scratch > g.scratch ? f.scratch : g.scratch;
 }
 
-template <int W, int S, bool LINK>
-static int launch_tri(const FusedArgs& a, const FusedPlan& f, cudaStream_t st) {
-  auto kern = k_tri_gram<W, S, LINK>;
-  NB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f.smem));
-  kern<<<(unsigned)(f.groups * f.C), (W + 1 + (LINK ? NAUX : 0)) * 32, f.smem, st>>>(a);
+template <int W, int S>
+static int launch_tri(int device, const FusedArgs& a, const FusedPlan& f, cudaStream_t st) {
+  auto kern = k_tri_gram<W, S>;
+  static KernelSetup setup;
+  int occ = 1;
+  if (int rc = setup.get(device, kern, (W + 1) * 32, (size_t)220 * 1024, &occ)) return rc;
+  kern<<<(unsigned)(f.groups * f.C), (W + 1) * 32, f.smem, st>>>(a);
   NB_LAUNCH_CHECK();
   return 0;
 }
 
-template <int S, bool LINK>
-static int launch_tri_w(const FusedArgs& a, const FusedPlan& f, cudaStream_t st) {
-  return f.W == 4 ? launch_tri<4, S, LINK>(a, f, st) : launch_tri<12, S, LINK>(a, f, st);
+template <int S>
+static int launch_tri_w(int device, const FusedArgs& a, const FusedPlan& f, cudaStream_t st) {
+  return f.W == 4 ? launch_tri<4, S>(device, a, f, st) : launch_tri<12, S>(device, a, f, st);
 }
 
-template <bool LINK>
-static int run_fused(int device, const FusedArgs& a0, const FusedPlan& f, double* stats, cudaStream_t st) {
-  int rc;
-  if (f.S == 6) rc = launch_tri_w<6, LINK>(a0, f, st);
-  else if (f.S == 5) rc = launch_tri_w<5, LINK>(a0, f, st);
-  else rc = launch_tri_w<4, LINK>(a0, f, st);
-  if (rc) return rc;
-  const int64_t d = a0.d;
-  int64_t total = d * (d + 1) / 2 + (LINK ? 2 * d + 3 : 0);
-  int64_t blocks = (total + 255) / 256;
-  k_fused_finish<<<(unsigned)(blocks < 592 ? blocks : 592), 256, 0, st>>>(a0, stats, LINK ? 0 : 1);
-  NB_LAUNCH_CHECK();
-  return 0;
-}
-
-// link == true : everything in one pass (eta, link, g, u and the triangular Gram).
-// link == false: only the upper-triangular X^T diag(w) X (w = wext, null = ones) into the d x d corner of stats.
-int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
-                    int ydt, const double* beta, const double* wext, bool link, double* stats, int64_t ldc,
-                    void* scratch, size_t scratch_bytes, cudaStream_t st) {
-  FusedPlan f = plan_fused(device, n, d, link);
-  NB_REQUIRE(scratch != nullptr && scratch_bytes >= f.scratch, "glm fused: scratch too small (%zu < %zu)",
+// Upper-triangular X^T diag(w) X (w = wext, null = ones), mirrored, into the d x d corner of `out` (row stride ldc).
+int tri_gram(int device, const double* x, int64_t n, int64_t d, int64_t ldx, const double* wext, double* out,
+             int64_t ldc, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  FusedPlan f = plan_fused(device, n, d);
+  NB_REQUIRE(scratch != nullptr && scratch_bytes >= f.scratch, "tri_gram: scratch too small (%zu < %zu)",
              scratch_bytes, f.scratch);
   FusedArgs a;
-  a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.y = y; a.ydt = ydt; a.beta = beta; a.wext = wext; a.family = family;
+  a.x = x; a.n = n; a.d = d; a.ldx = ldx; a.wext = wext;
   a.nblk = f.nblk; a.T = f.T; a.C = f.C; a.KG = f.KG; a.groups = f.groups; a.rows_per_group = f.rows_per_group;
   a.ldc = ldc;
-  a.skip_obj = getenv("NUMS_B200_SKIP_OBJ") ? 1 : 0;
   a.part_h = (double*)scratch;
-  a.part_v = (double*)((char*)scratch + f.off_v);
-  return link ? run_fused<true>(device, a, f, stats, st) : run_fused<false>(device, a, f, stats, st);
+  int rc = f.S == 5 ? launch_tri_w<5>(device, a, f, st) : launch_tri_w<4>(device, a, f, st);
+  if (rc) return rc;
+  const int64_t blocks = (d * (d + 1) / 2 + 255) / 256;
+  k_fused_finish<<<(unsigned)(blocks < 592 ? blocks : 592), 256, 0, st>>>(a, out);
+  NB_LAUNCH_CHECK();
+  return 0;
 }
 
 }  // namespace nb

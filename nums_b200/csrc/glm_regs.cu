@@ -240,7 +240,7 @@ k_regs_finish(int64_t d, int nparts, const double* __restrict__ parts, double* _
 
 // Newton statistics fit a warp's registers up to d = 64; the gradient-only pass (no tiles) up to d = 192
 bool glm_regs_applicable(int64_t d, int want_hess) {
-  return d >= 8 && d <= (want_hess ? 64 : 192) && !getenv("NUMS_B200_NO_REGS");
+  return d >= 8 && d <= (want_hess ? 64 : 192) && !NB_ENV_FLAG("NUMS_B200_NO_REGS");
 }
 
 constexpr int RG_MAX_CTAS_PER_SM = 8;
@@ -268,9 +268,8 @@ static int launch_regs(int device, const RegsArgs& a, double* stats, cudaStream_
   // one resident wave: as many CTAs per SM as the kernel's registers allow (the narrow variants need the extra
   // warps to keep enough loads in flight)
   int per_sm = 1;
-  NB_CHECK(cudaFuncSetAttribute(k_glm_regs<NB, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  NB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_glm_regs<NB, MODE>, RG_THREADS, smem));
-  if (per_sm < 1) per_sm = 1;
+  static KernelSetup setup;
+  if (int rc = setup.get(device, k_glm_regs<NB, MODE>, RG_THREADS, smem, &per_sm)) return rc;
   if (per_sm > RG_MAX_CTAS_PER_SM) per_sm = RG_MAX_CTAS_PER_SM;
   int ctas = dev_info(device).sms * per_sm;
   if (want < ctas) ctas = (int)(want < 1 ? 1 : want);
@@ -306,7 +305,7 @@ int glm_regs_stats(int device, int family, const double* x, int64_t n, int64_t d
 
 // First pass of the two-pass Newton statistics for 64 < d <= 160 (beyond that the accumulators spill): g, u, sum r, sum w, objective into `stats`, the
 // weights into wbuf (null for the linear family, whose weights are 1); glm_fused.cu adds X^T diag(w) X.
-bool glm_regs_pass1_applicable(int64_t d) { return d > 64 && d <= 160 && !getenv("NUMS_B200_NO_REGS"); }
+bool glm_regs_pass1_applicable(int64_t d) { return d > 64 && d <= 160 && !NB_ENV_FLAG("NUMS_B200_NO_REGS"); }
 
 int glm_regs_pass1(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                    const double* beta, int skip_obj, double* wbuf, double* stats, void* scratch, size_t scratch_bytes,

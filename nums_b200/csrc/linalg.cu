@@ -310,7 +310,7 @@ int nb_glm_newton_update(int device, int64_t p, double* stats_d, const double* l
   k_newton_prep<<<1, 256, 0, st>>>(p, stats_d, l2vec_d, beta_d, gmax_d);
   NB_LAUNCH_CHECK();
   const int* gate = nullptr;
-  if (p >= 2 && !getenv("NUMS_B200_NEWTON_INVERSE")) {
+  if (p >= 2 && !NB_ENV_FLAG("NUMS_B200_NEWTON_INVERSE")) {
     // H = L L^T, two substitutions (newton_chol.cu); the pivoted inverse below runs only if H is not positive definite
     int rc = newton_chol_solve(device, p, stats_d, hinv, stats_d + p * p, beta_d, beta_out_d, z, flag, info_d, st);
     if (rc) return rc;

@@ -824,9 +824,8 @@ static bool ws_transpose_ok(const WsPlan& wp, int64_t m, int64_t n, int64_t k) {
 // glm_fused.cu: warp-specialised upper-triangular X^T diag(w) X for 8 <= d <= 256
 bool fused_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
-int glm_fused_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y,
-                    int ydt, const double* beta, const double* wext, bool link, double* stats, int64_t ldc,
-                    void* scratch, size_t scratch_bytes, cudaStream_t st);
+int tri_gram(int device, const double* x, int64_t n, int64_t d, int64_t ldx, const double* wext, double* out,
+             int64_t ldc, void* scratch, size_t scratch_bytes, cudaStream_t st);
 
 size_t gemm_scratch_bytes(int device, int64_t m, int64_t n, int64_t k) {
   if (m <= 0 || n <= 0 || k <= 0) return 0;
@@ -874,9 +873,8 @@ int gemm_f64(int device, int64_t m, int64_t n, int64_t k, const double* a, int64
   g.w = w; g.c = c; g.ldc = ldc;
   const bool sym = (a == b) && (m == n) && a_mc && b_nc && (a_cs == b_rs);
   if (sym && fused_applicable(k, n, a_cs, a) && scratch != nullptr && scratch_bytes >= fused_scratch_bytes(device, k, n))
-    return glm_fused_stats(device, 0, a, k, n, a_cs, nullptr, NB_F64, nullptr, w, false, c, ldc, scratch,
-                           scratch_bytes, st);
-  if (!getenv("NUMS_B200_NO_WS") && !(a_mc && b_nc) && !sym && !getenv("NUMS_B200_NO_WS_TRANSPOSE")) {
+    return tri_gram(device, a, k, n, a_cs, w, c, ldc, scratch, scratch_bytes, st);
+  if (!NB_ENV_FLAG("NUMS_B200_NO_WS") && !(a_mc && b_nc) && !sym && !NB_ENV_FLAG("NUMS_B200_NO_WS_TRANSPOSE")) {
     // large product with a k-contiguous operand: copy it into the [k][.] layout, then take the fast variant
     const WsPlan wp = ws_plan(device, m, n, k, false, true);
     const size_t need = mm_up((size_t)m * k * 8) + mm_up((size_t)k * n * 8);
@@ -902,7 +900,7 @@ int gemm_f64(int device, int64_t m, int64_t n, int64_t k, const double* a, int64
         return gemm_ws_f64(wp, m, n, k, a2, lda2, true, b2, ldb2, true, w, c, ldc, nullptr, st);
     }
   }
-  if (!getenv("NUMS_B200_NO_WS") && gemm_ws_aligned(a, g.lda, b, g.ldb, w, c, ldc)) {
+  if (!NB_ENV_FLAG("NUMS_B200_NO_WS") && gemm_ws_aligned(a, g.lda, b, g.ldb, w, c, ldc)) {
     const WsPlan wp = ws_plan(device, m, n, k, sym, a_mc && b_nc);
     if (wp.ok && (wp.scratch == 0 || (scratch != nullptr && scratch_bytes >= wp.scratch))) {
       int rc = gemm_ws_f64(wp, m, n, k, a, g.lda, a_mc, b, g.ldb, b_nc, w, c, ldc, (double*)scratch, st);

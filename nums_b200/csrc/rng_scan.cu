@@ -20,6 +20,7 @@
 // geometry.  Ziggurat states: S (fresh word), W (wedge test pending on the previous word), T1/T2 (tail loop, first /
 // second uniform of a pair) with the sign bit of the word that entered the tail.
 #include "pcg64.cuh"
+#include "libm_exact.cuh"
 #define NB_ZIG_QUAL static __device__
 #include "zig_tables.h"
 
@@ -73,8 +74,8 @@ __device__ __forceinline__ bool zig_step(int& st, uint64_t w, uint64_t prev, dou
   }
   if (base == ZT1) { st = (st & ~3) | ZT2; return false; }
   // ZT2: the pair (prev, w)
-  const double xx = __dmul_rn(-NB_ZIG_INV_R, log1p(-u53(prev)));
-  const double yy = -log1p(-u53(w));
+  const double xx = __dmul_rn(-NB_ZIG_INV_R, nb_libm::log1p_glibc_fma(-u53(prev)));
+  const double yy = -nb_libm::log1p_glibc_fma(-u53(w));
   if (__dadd_rn(yy, yy) > __dmul_rn(xx, xx)) {
     const double t = __dadd_rn(NB_ZIG_R, xx);
     val = (st & ZSIGN) ? -t : t;

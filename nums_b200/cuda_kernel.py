@@ -226,7 +226,7 @@ def _cholqr_pass(K, Y, dev, shift=0.0):
         _lib.check(_lib.load().nb_eye(dev, n, n, eye.ptr, eye.code, dv.stream_ptr(dev)))
         G = K.bop("add", G, K.bop("mul", eye, dv.from_numpy(np.float64(shift), dev), False, False, {}),
                      False, False, {})
-    L = _chol_lower(self, G, dev)
+    L = _chol_lower(K, G, dev)
     if L is None:
         return None
     R = dv.contiguous(L.T)
