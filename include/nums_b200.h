@@ -299,6 +299,31 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
                  const void* y_d, int ydt, const double* beta_d, int want_hess,
                  double* stats_d, void* scratch_d, size_t scratch_bytes, void* stream);
 
+/* The same statistics with the d x d part of the Hessian, X^T diag(w) X (glms.py:491-499: the
+ * `(X.T * s) @ X` of LogisticRegression.hessian, the Gram matrix of LinearRegression), formed on the
+ * INTEGER tensor path (tcgen05.mma kind::i8, int32 accumulators in tensor memory) instead of FP64 DMMA:
+ * x sqrt(w) is rounded to a 39-bit fixed-point number per column scale and split into five int8 digit
+ * planes whose pairwise products are exact; relative error <= ~1e-11 of the column scale (see
+ * csrc/glm_ozaki.cu).  Requested with want_hess | NB_GLM_INT8_HESSIAN (also in nb_glm_scratch_bytes: the
+ * planes need 5 bytes per element of X) and the output of nb_glm_prepare for this X block; applies to
+ * logistic / linear families, 128 < d <= 256, d % 4 == 0, ldx % 4 == 0, 32-byte aligned X — otherwise
+ * the call takes the FP64 path of nb_glm_stats.  A value outside the prepared column scale (prep of
+ * another block, Inf/NaN in X) turns H into NaN instead of a wrong number.
+ *
+ * nb_glm_prepare: per-column maxima of |X| -> power-of-two scales (one pass over X; X blocks are immutable,
+ * numpy_kernel.py:131-135, so once per block).  prep_d: nb_glm_prep_bytes(d) bytes of device memory.  Its first
+ * 258 int32 are readable by the host: colexp[256] (max|x[:,i]| < 2^colexp[i]), bad (Inf/NaN seen), range_log2 =
+ * ceil(log2(max_i max|x[:,i]| / rms(x[:,i]))).  The fixed-point error of H, relative to sqrt(H_ii H_jj), is about
+ * 2^-38 * 2^range_log2 (less by ~sqrt(n) for rounding errors of random sign); a caller that needs 1e-10 should
+ * take the FP64 path when range_log2 > 5 (heavy-tailed columns, single outliers). */
+#define NB_GLM_INT8_HESSIAN 4
+size_t nb_glm_prep_bytes(int64_t d);
+int nb_glm_prepare(int device, const double* x_d, int64_t n, int64_t d, int64_t ldx, void* prep_d,
+                   size_t prep_bytes, void* stream);
+int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx,
+                          const void* y_d, int ydt, const double* beta_d, int want_hess, const void* prep_d,
+                          double* stats_d, void* scratch_d, size_t scratch_bytes, void* stream);
+
 /* The Newton update of glms.py:660-676 on the (all-reduced) packed stats:
  *     g += l2vec * beta;  H += diag(l2vec)           (grad_penalty/hessian_penalty :254-272)
  *     beta_out = beta - inv(H) @ g                    (explicit inverse, linalg.py:246-261)

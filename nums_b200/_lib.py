@@ -68,6 +68,10 @@ SIGNATURES = {
     "nb_glm_stats_len": (c_i64, [c_i64]),
     "nb_glm_scratch_bytes": (c_sz, [c_int, c_i64, c_i64, c_int]),
     "nb_glm_stats": (c_int, [c_int, c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_sz, c_vp]),
+    "nb_glm_prep_bytes": (c_sz, [c_i64]),
+    "nb_glm_prepare": (c_int, [c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_sz, c_vp]),
+    "nb_glm_stats_prepared": (c_int, [c_int, c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_int, c_vp, c_int, c_vp, c_vp,
+                                      c_vp, c_sz, c_vp]),
     "nb_glm_newton_scratch_bytes": (c_sz, [c_i64]),
     "nb_glm_newton_update": (c_int, [c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "nb_glm_predict": (c_int, [c_int, c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp]),

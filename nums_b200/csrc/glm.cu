@@ -389,12 +389,19 @@ size_t fused_scratch_bytes(int device, int64_t n, int64_t d);
 int tri_gram(int device, const double* x, int64_t n, int64_t d, int64_t ldx, const double* wext, double* out,
              int64_t ldc, void* scratch, size_t scratch_bytes, cudaStream_t st);
 
+// glm_ozaki.cu: X^T diag(w) X on the int8 tensor path (tcgen05), 128 < d <= 256
+bool oz_applicable(int family, int64_t n, int64_t d, int64_t ldx, const double* x);
+size_t oz_scratch_bytes(int device, int64_t n);
+int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                 const double* beta, int skip_obj, const void* prep, double* stats, double* parts, int max_parts,
+                 int* nparts, void* scratch, size_t scratch_bytes, cudaStream_t st);
+
 struct GlmLayout {
-  size_t off_w, off_parts, off_gemm, total;
+  size_t off_w, off_parts, off_gemm, off_oz, total;
   int max_parts;
 };
 
-static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
+static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess, bool int8_hess = false) {
   GlmLayout L;
   const int sms = dev_info(device).sms;
   L.max_parts = sms * 4;
@@ -419,6 +426,8 @@ static GlmLayout glm_layout(int device, int64_t n, int64_t d, int want_hess) {
     size_t r = align256(glm_regs_scratch_bytes(device, d, want_hess));
     if (r > cur) cur = r;
   }
+  L.off_oz = cur;
+  if (int8_hess && want_hess && d > 128 && d <= 256) cur += oz_scratch_bytes(device, n);
   L.total = cur;
   return L;
 }
@@ -501,20 +510,29 @@ extern "C" {
 int64_t nb_glm_stats_len(int64_t d) { int64_t p = d + 1; return p * p + p + 1; }
 
 size_t nb_glm_scratch_bytes(int device, int64_t n, int64_t d, int want_hess) {
-  return glm_layout(device, n, d, want_hess & 1).total;
+  return glm_layout(device, n, d, want_hess & 1, (want_hess & NB_GLM_INT8_HESSIAN) != 0).total;
 }
 
 int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx, const void* y_d,
                  int ydt, const double* beta_d, int want_hess, double* stats_d, void* scratch_d,
                  size_t scratch_bytes, void* stream) {
+  return nb_glm_stats_prepared(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, nullptr, stats_d, scratch_d,
+                               scratch_bytes, stream);
+}
+
+int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx, const void* y_d,
+                          int ydt, const double* beta_d, int want_hess, const void* prep_d, double* stats_d,
+                          void* scratch_d, size_t scratch_bytes, void* stream) {
   NB_ENTER(device);
   NB_REQUIRE(family >= NB_GLM_LINEAR && family <= NB_GLM_LOGISTIC_IRLS, "nb_glm_stats: unknown family %d", family);
   NB_REQUIRE(d >= 1 && n >= 0 && ldx >= d, "nb_glm_stats: bad shape n=%lld d=%lld ldx=%lld", (long long)n,
              (long long)d, (long long)ldx);
   NB_REQUIRE(ydt == NB_F64 || ydt == NB_I64, "nb_glm_stats: y dtype %d not supported", ydt);
   const int skip_obj = (want_hess & 2) ? 1 : 0;      // NB_GLM_NO_OBJECTIVE
+  const bool int8_hess = (want_hess & NB_GLM_INT8_HESSIAN) != 0;
   want_hess &= 1;
-  GlmLayout L = glm_layout(device, n, d, want_hess);
+  NB_REQUIRE(!int8_hess || prep_d != nullptr, "nb_glm_stats: NB_GLM_INT8_HESSIAN needs the block's nb_glm_prepare output");
+  GlmLayout L = glm_layout(device, n, d, want_hess, int8_hess);
   NB_REQUIRE(scratch_d != nullptr && scratch_bytes >= L.total, "nb_glm_stats: scratch too small (%zu < %zu)",
              scratch_bytes, L.total);
   char* sc = (char*)scratch_d;
@@ -529,6 +547,17 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
   }
   if (glm_regs_applicable(d, want_hess))
     return glm_regs_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, want_hess, skip_obj, stats_d, sc, L.total, st);
+  if (int8_hess && want_hess && oz_applicable(family, n, d, ldx, x_d)) {
+    // pass A (link, g, u, digit planes) + pass B (int8 tensor products) + finish; the vector statistics go through
+    // the same second stage as k_glm_rows
+    int np = 0;
+    int rc = oz_glm_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, skip_obj, prep_d, stats_d, parts, L.max_parts,
+                          &np, sc + L.off_oz, L.total - L.off_oz, st);
+    if (rc) return rc;
+    k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, np, parts, want_hess, stats_d);
+    NB_LAUNCH_CHECK();
+    return 0;
+  }
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);
   GlmRowsArgs a;
   a.x = x_d; a.n = n; a.d = d; a.ldx = ldx; a.y = y_d; a.ydt = ydt; a.beta = beta_d;

@@ -1,0 +1,727 @@
+// The Hessian X^T diag(w) X of the Newton step (nums/models/glms.py:491-499) for 128 < d <= 256 on the INTEGER tensor
+// path of sm_100a (tcgen05.mma kind::i8, int32 accumulators in tensor memory), exact to ~2^-40 of the largest
+// entry of each column: an Ozaki-style error-free split.
+//
+// Why: FP64 has no tcgen05 kind; the DMMA pipe peaks at 37 TFLOP/s, which holds X^T W X at d = 256 to 28 ms per
+// 1.25e7-row shard (k_tri_gram, 88 % of that peak) while the bytes take 4 ms.  The int8 path is ~100x faster per
+// multiply, so a handful of exact integer products replace one FP64 product.
+//
+// Scheme.  With per-column powers of two 2^q_i (from the column maxima of |X|, computed once per block:
+// nb_glm_prepare) every a_ki = x_ki * sqrt(w_k) is rounded to a 39-bit integer v_ki = rint(a_ki 2^q_i) and written as
+// five balanced base-256 digits v = sum_p d_p 256^(4-p), d_p in [-128, 127] ("planes" p = 0..4 of int8, plane 0 most
+// significant).  Then sum_k v_ki v_kj = sum_L 256^(8-L) S_L with S_L = sum over ordered digit pairs p + p' = L of the
+// plane products P_pp' = plane_p^T plane_p'.  Every P is an exact int8 x int8 -> int32 tensor product (at most 32768
+// rows per accumulation: 2 * 2^14 * 2^15 < 2^31).  Levels L <= 5 are kept (11 products, using P_p'p = P_pp'^T); the
+// dropped levels are below 2^-48 of the column scale squared.  Rounding to v is the approximation that matters:
+// half a unit in 2^-38 of the column maximum per element.
+//
+//   pass A  k_oz_rows    reads X once (HBM-bound): eta, link, g, u, sum w as k_glm_rows does, and writes the five digit
+//                        planes [plane][row][256] (5 bytes per element instead of the 8 of w or of X*sqrt(w)).
+//   pass B  k_oz_gemm    CTA pairs (cta_group::2, M = 256, N = 256): TMA tensor copies (128-byte swizzle) bring
+//                        [64 rows][128 bytes] tiles of the planes a pair needs, one elected thread issues
+//                        tcgen05.mma kind::i8 on MN-major operands, the accumulators of two "slots" fill the 512
+//                        tensor-memory columns.  Eight slots are needed (a slot holds same-level products of one
+//                        kind: P_pp' with p < p' enter H as P + P^T, P_pp once), so four groups of pairs work on the
+//                        same rows at about the same time and share most plane reads in L2 (measured DRAM traffic:
+//                        1.4x the planes; holding the pairs in lock step through global progress counters brought it to
+//                        1.0x and cost 2.5x in time, and was removed).  Epilogue warps read the
+//                        accumulators (tcgen05.ld) after each range of rows and store them as int32 partials.
+//   finish  k_oz_reduce  sums the partials exactly (int64);  k_oz_finish applies 256^(8-L) and 2^(-q_i-q_j), mirrors.
+//
+// A value that does not fit the 39 bits (the prepared column maxima do not belong to this X, or X holds Inf/NaN)
+// raises a flag that turns H into NaN: the caller's solve reports it; nothing is silently wrong.
+#include "glm_common.cuh"
+#include <cuda.h>
+#include <mutex>
+
+namespace nb {
+
+constexpr int OZ_S = 5;                 // digit planes
+constexpr int OZ_COLS = 256;            // plane width (columns of X, zero padded)
+constexpr int OZ_HALF = 128;
+constexpr int OZ_KC = 64;               // rows per pipeline stage
+constexpr int OZ_TILES = 20;              // 8 KB tiles of shared memory: a group with np planes runs OZ_TILES / np stages
+constexpr int OZ_MAX_STAGES = 8;
+constexpr int OZ_MAX_RANGE = 32768;     // rows per accumulation (int32 headroom)
+constexpr int OZ_GROUPS = 4;
+constexpr int OZ_SLOTS = 2;
+constexpr uint32_t OZ_TILE = OZ_KC * OZ_HALF;           // 8 KB: one plane, one column half, one stage
+constexpr int OZ_ROWS_THREADS = 256;
+constexpr int OZ_R = 4;                 // rows per warp step in pass A
+constexpr int OZ_VBITS = 38;            // |v| < 2^38
+
+// products of each group: {slot, plane of A, plane of B}; planes the group stages.  Levels 0..5 (11 products, 8 slots:
+// the first dropped terms, level 6, are 2^-48 of the column scale squared).
+struct OzProduct { int slot, pa, pb; };
+// Grouping rule: no group stages more than four planes (the TMA tensor copies of a stage, 64 x 128-byte rows per plane and
+// CTA, are the tighter budget: five planes per stage held the whole kernel to the pace of that one group).
+__constant__ OzProduct c_oz_products[OZ_GROUPS][3] = {
+    {{0, 0, 3}, {0, 1, 2}, {1, 0, 0}},       // level 3 | level 0
+    {{0, 0, 4}, {0, 1, 3}, {1, 0, 1}},       // level 4, pairs p < p' | level 1
+    {{0, 1, 4}, {0, 2, 3}, {1, 2, 2}},       // level 5 | level 4, (2,2)
+    {{0, 0, 2}, {1, 1, 1}, {-1, 0, 0}},      // level 2: (0,2) | (1,1)
+};
+__constant__ int c_oz_nplanes[OZ_GROUPS] = {4, 4, 4, 3};
+__constant__ int c_oz_planes[OZ_GROUPS][4] = {{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 3, 4}, {0, 1, 2, 0}};
+// slot (group, s) -> level and kind (1 = pairs p < p': enters as P + P^T; 0 = p == p')
+constexpr int OZ_LEVELS = 6;
+__constant__ int c_oz_slot_level[OZ_GROUPS][OZ_SLOTS] = {{3, 0}, {4, 1}, {5, 4}, {2, 2}};
+__constant__ int c_oz_slot_off[OZ_GROUPS][OZ_SLOTS] = {{1, 0}, {1, 1}, {1, 0}, {1, 0}};
+
+struct OzPrep {               // nb_glm_prepare output (device memory)
+  int32_t colexp[OZ_COLS];    // max|x[:, i]| < 2^colexp[i];  INT32_MIN for an all-zero column
+  int32_t bad;                // non-finite entry seen
+  int32_t range_log2;         // ceil(log2(max_i max|x[:, i]| / rms(x[:, i]))): how many leading bits the largest entries cost
+  int32_t pad[62];
+};
+constexpr int OZ_PREP_CTAS = 592;
+
+// ------------------------------------------------------------------------------------------------ prepare
+// Column maxima of |X| (-> the fixed-point scale of each column) and column sums of squares (-> how far the typical
+// entry sits below that scale; fixed summation order, so the verdict does not change from run to run).
+__global__ void __launch_bounds__(256)
+k_oz_colmax(const double* __restrict__ x, int64_t n, int64_t d, int64_t ldx, unsigned long long* __restrict__ maxbits,
+            double* __restrict__ sumsq) {
+  const int c = threadIdx.x;
+  unsigned long long m = 0;
+  double q0 = 0.0, q1 = 0.0, q2 = 0.0, q3 = 0.0;
+  if (c < d) {
+    const int64_t stride = gridDim.x;
+    int64_t r = blockIdx.x;
+    for (; r + 3 * stride < n; r += 4 * stride) {
+      const double v0 = x[r * ldx + c], v1 = x[(r + stride) * ldx + c], v2 = x[(r + 2 * stride) * ldx + c],
+                   v3 = x[(r + 3 * stride) * ldx + c];
+      const unsigned long long a0 = (unsigned long long)__double_as_longlong(fabs(v0));
+      const unsigned long long a1 = (unsigned long long)__double_as_longlong(fabs(v1));
+      const unsigned long long a2 = (unsigned long long)__double_as_longlong(fabs(v2));
+      const unsigned long long a3 = (unsigned long long)__double_as_longlong(fabs(v3));
+      m = max(max(m, a0), max(a1, max(a2, a3)));
+      q0 = fma(v0, v0, q0); q1 = fma(v1, v1, q1); q2 = fma(v2, v2, q2); q3 = fma(v3, v3, q3);
+    }
+    for (; r < n; r += stride) {
+      const double v = x[r * ldx + c];
+      m = max(m, (unsigned long long)__double_as_longlong(fabs(v)));
+      q0 = fma(v, v, q0);
+    }
+    atomicMax(&maxbits[c], m);      // non-negative doubles order like their bit patterns (NaN patterns sort above Inf)
+  }
+  sumsq[(size_t)blockIdx.x * OZ_COLS + c] = (q0 + q1) + (q2 + q3);
+}
+
+__global__ void k_oz_colexp(const unsigned long long* __restrict__ maxbits, const double* __restrict__ sumsq, int nparts,
+                            int64_t n, int64_t d, OzPrep* __restrict__ prep) {
+  const int c = threadIdx.x;
+  int bad = 0, range = 0;
+  if (c < OZ_COLS) {
+    int e = INT32_MIN;
+    if (c < d) {
+      const unsigned long long b = maxbits[c];
+      if (b >= 0x7ff0000000000000ull) bad = 1;
+      else if (b != 0) {
+        const double m = __longlong_as_double((long long)b);
+        int ex;
+        frexp(m, &ex);            // m = f 2^ex, f in [0.5, 1)  =>  m < 2^ex
+        e = ex;
+        double ss = 0.0;
+        for (int k = 0; k < nparts; k++) ss += sumsq[(size_t)k * OZ_COLS + c];
+        const double rms = sqrt(ss / (double)(n > 0 ? n : 1));
+        if (rms > 0.0 && isfinite(rms)) range = (int)ceil(log2(m / rms));
+      }
+    }
+    prep->colexp[c] = e;
+  }
+  bad = __syncthreads_or(bad);
+  __shared__ int s_range;
+  if (c == 0) s_range = 0;
+  __syncthreads();
+  atomicMax(&s_range, range);
+  __syncthreads();
+  if (c == 0) { prep->bad = bad; prep->range_log2 = s_range; }
+}
+
+// ------------------------------------------------------------------------------------------------ pass A
+struct OzRowsArgs {
+  const double* x; int64_t n, d, ldx;
+  const void* y; int ydt;
+  const double* beta;
+  int family, skip_obj;
+  int ew;                       // sqrt(w) <= 2^ew for this family
+  const OzPrep* prep;
+  int8_t* planes; int64_t plane_stride;     // plane p at planes + p * plane_stride, row k at + k * 256
+  double* partials;             // [gridDim.x][2*d + 3]  (layout of k_glm_rows, summed by k_glm_rows_finish)
+  int* flag;                    // set when a value leaves the 39-bit range
+};
+
+__device__ __forceinline__ void ld256(const double* p, double& a, double& b, double& c, double& d) {
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+
+__global__ void __launch_bounds__(OZ_ROWS_THREADS, 1)
+k_oz_rows(const OzRowsArgs a) {
+  constexpr int NW = OZ_ROWS_THREADS / 32;
+  constexpr int R = OZ_R;
+  __shared__ double s_g[OZ_COLS], s_u[OZ_COLS], s_sc[4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t d = a.d, n = a.n;
+  for (int j = tid; j < OZ_COLS; j += OZ_ROWS_THREADS) { s_g[j] = 0.0; s_u[j] = 0.0; }
+  if (tid < 4) s_sc[tid] = 0.0;
+  __syncthreads();
+
+  // this lane owns columns cA..cA+3 and cB..cB+3 (element slots 0..3 and 4..7)
+  const int cA = 4 * lane, cB = OZ_HALF + 4 * lane;
+  const bool vA = cA < d, vB = cB < d;             // d is a multiple of 4
+  double bet[8], cs[8];
+#pragma unroll
+  for (int e = 0; e < 8; e++) {
+    const int col = (e < 4 ? cA : cB) + (e & 3);
+    bet[e] = col < d ? a.beta[col] : 0.0;
+    const int ce = a.prep->colexp[col];
+    // v = x sqrt(w) 2^q with q = VBITS - colexp - ew, so that |v| < 2^VBITS
+    int q = OZ_VBITS - ce - a.ew;
+    cs[e] = (col < d && ce != INT32_MIN && q < 1000 && q > -1000) ? scalbn(1.0, q) : 0.0;
+  }
+  const double beta0 = a.beta[d];
+  // 1.5 * 2^52 + sum_s 128 * 256^s: after fma(x, scale, MAGIC) the low 40 mantissa bits are v + bias, i.e. the
+  // bytes d_s + 128 of the balanced base-256 digits of v (round to nearest even comes with the fma)
+  const double MAGIC = 6755399441055744.0 + 551911719040.0;
+
+  double g[8], u[8];
+#pragma unroll
+  for (int e = 0; e < 8; e++) { g[e] = 0.0; u[e] = 0.0; }
+  double gi = 0.0, ui = 0.0, ob = 0.0;
+  uint32_t bad = 0;
+
+  const int64_t nbatches = (n + R - 1) / R;
+  const int64_t per_it = (int64_t)gridDim.x * NW;
+  for (int64_t batch = (int64_t)blockIdx.x * NW + warp; batch < nbatches; batch += per_it) {
+    const int64_t row0 = batch * R;
+    double xv[R][8];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int64_t row = row0 + r;
+      const double* xr = a.x + row * a.ldx;
+      if (row < n && vA) ld256(xr + cA, xv[r][0], xv[r][1], xv[r][2], xv[r][3]);
+      else { xv[r][0] = xv[r][1] = xv[r][2] = xv[r][3] = 0.0; }
+      if (row < n && vB) ld256(xr + cB, xv[r][4], xv[r][5], xv[r][6], xv[r][7]);
+      else { xv[r][4] = xv[r][5] = xv[r][6] = xv[r][7] = 0.0; }
+    }
+    double part[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int e = 0; e < 4; e++) { s0 = fma(xv[r][e], bet[e], s0); s1 = fma(xv[r][4 + e], bet[4 + e], s1); }
+      double s = s0 + s1;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      part[r] = s;
+    }
+    double eta = part[0];
+#pragma unroll
+    for (int r = 1; r < R; r++) if ((lane % R) == r) eta = part[r];
+    eta += beta0;
+    const int64_t myrow = row0 + (lane % R);
+    const bool inb = myrow < n;
+    const double yv = inb ? load_y(a.y, a.ydt, myrow) : 0.0;
+    LinkOut lo = a.skip_obj ? glm_link_noobj_rt(a.family, eta, yv) : glm_link_rt(a.family, eta, yv);
+    if (!inb) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
+    const double sw = sqrt(lo.wgt);
+    if (lane < R && inb) { ob += lo.obj; gi += lo.resid; ui += lo.wgt; }
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const double rr = __shfl_sync(0xffffffffu, lo.resid, r);
+      const double ww = __shfl_sync(0xffffffffu, lo.wgt, r);
+      const double sq = __shfl_sync(0xffffffffu, sw, r);
+      uint32_t lo32[8], hi32[8];
+#pragma unroll
+      for (int e = 0; e < 8; e++) {
+        g[e] = fma(rr, xv[r][e], g[e]);
+        u[e] = fma(ww, xv[r][e], u[e]);
+        const double t = fma(xv[r][e], __dmul_rn(sq, cs[e]), MAGIC);
+        lo32[e] = (uint32_t)__double2loint(t);
+        hi32[e] = (uint32_t)__double2hiint(t);
+        bad |= (hi32[e] ^ 0x43380000u) & 0xffffff00u;
+      }
+      const int64_t row = row0 + r;
+      if (row < n) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const uint32_t* L = lo32 + 4 * h;
+          const uint32_t* H = hi32 + 4 * h;
+          // 4x4 byte transpose of the low words: w_s = {byte s of element 0, 1, 2, 3}
+          const uint32_t t01a = prmt(L[0], L[1], 0x5140), t01b = prmt(L[0], L[1], 0x7362);
+          const uint32_t t23a = prmt(L[2], L[3], 0x5140), t23b = prmt(L[2], L[3], 0x7362);
+          const uint32_t w0 = prmt(t01a, t23a, 0x5410), w1 = prmt(t01a, t23a, 0x7632);
+          const uint32_t w2 = prmt(t01b, t23b, 0x5410), w3 = prmt(t01b, t23b, 0x7632);
+          const uint32_t w4 = prmt(prmt(H[0], H[1], 0x0040), prmt(H[2], H[3], 0x0040), 0x5410);
+          int8_t* base = a.planes + row * OZ_COLS + (h ? cB : cA);
+          if (h ? vB : vA) {
+            // plane p holds digit s = 4 - p; signed digit = byte ^ 0x80
+            *reinterpret_cast<uint32_t*>(base + 0 * a.plane_stride) = w4 ^ 0x80808080u;
+            *reinterpret_cast<uint32_t*>(base + 1 * a.plane_stride) = w3 ^ 0x80808080u;
+            *reinterpret_cast<uint32_t*>(base + 2 * a.plane_stride) = w2 ^ 0x80808080u;
+            *reinterpret_cast<uint32_t*>(base + 3 * a.plane_stride) = w1 ^ 0x80808080u;
+            *reinterpret_cast<uint32_t*>(base + 4 * a.plane_stride) = w0 ^ 0x80808080u;
+          } else {
+            // columns beyond d: the planes are read 256 wide, keep them zero
+#pragma unroll
+            for (int p = 0; p < OZ_S; p++) *reinterpret_cast<uint32_t*>(base + p * a.plane_stride) = 0u;
+          }
+        }
+      }
+    }
+  }
+  if (bad) atomicExch(a.flag, 1);
+
+  // CTA reduction in warp order (deterministic)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    gi += __shfl_down_sync(0xffffffffu, gi, o);
+    ui += __shfl_down_sync(0xffffffffu, ui, o);
+    ob += __shfl_down_sync(0xffffffffu, ob, o);
+  }
+  for (int q = 0; q < NW; q++) {
+    if (warp == q) {
+#pragma unroll
+      for (int e = 0; e < 8; e++) {
+        const int col = (e < 4 ? cA : cB) + (e & 3);
+        s_g[col] += g[e]; s_u[col] += u[e];
+      }
+      if (lane == 0) { s_sc[0] += gi; s_sc[1] += ui; s_sc[2] += ob; }
+    }
+    __syncthreads();
+  }
+  double* out = a.partials + (size_t)blockIdx.x * (2 * d + 3);
+  for (int64_t j = tid; j < d; j += OZ_ROWS_THREADS) { out[j] = s_g[j]; out[d + j] = s_u[j]; }
+  if (tid == 0) { out[2 * d] = s_sc[0]; out[2 * d + 1] = s_sc[1]; out[2 * d + 2] = s_sc[2]; }
+}
+
+// ------------------------------------------------------------------------------------------------ pass B
+__device__ __forceinline__ uint32_t oz_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void oz_mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(oz_smem(bar)), "r"(count));
+}
+__device__ __forceinline__ void oz_mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(oz_smem(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void oz_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(oz_smem(bar)) : "memory");
+}
+// arrive on the same barrier of CTA `rank` of the cluster
+__device__ __forceinline__ void oz_mbar_arrive_remote(uint64_t* bar, uint32_t rank) {
+  asm volatile("{\n\t.reg .b32 ra;\n\tmapa.shared::cluster.u32 ra, %0, %1;\n\tmbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+               :: "r"(oz_smem(bar)), "r"(rank) : "memory");
+}
+__device__ __forceinline__ void oz_mbar_wait(uint64_t* bar, unsigned parity) {
+  const uint32_t addr = oz_smem(bar);
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      :: "r"(addr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint32_t oz_cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void oz_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared-memory matrix descriptor, MN-major operand with the 128-byte swizzle: atoms of 8 rows x 128 bytes, groups of
+// 8 rows (K) are 1024 bytes apart; one atom along MN (the CTA's 128 columns)
+__device__ __forceinline__ uint64_t oz_desc(uint32_t saddr) {
+  uint64_t dsc = 0;
+  dsc |= (uint64_t)((saddr >> 4) & 0x3fff);
+  dsc |= (uint64_t)((OZ_TILE >> 4) & 0x3fff) << 16;      // leading byte offset (unused: one atom along MN)
+  dsc |= (uint64_t)((8 * OZ_HALF) >> 4) << 32;           // stride byte offset: next group of 8 rows
+  dsc |= (uint64_t)1 << 46;                              // descriptor version
+  dsc |= (uint64_t)2 << 61;                              // SWIZZLE_128B
+  return dsc;
+}
+// instruction descriptor, kind::i8: D = s32, A = B = signed 8 bit, both MN-major, M = 256 (pair), N = 256
+constexpr uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((256u >> 3) << 17) | ((256u >> 4) << 24);
+
+struct OzGemmArgs {
+  int64_t n;
+  int range_rows;           // rows per accumulation item (multiple of OZ_KC)
+  int nranges;
+  int lanes;                // pairs per group
+  int32_t* part;            // [nranges][OZ_GROUPS][OZ_SLOTS][256][256]
+};
+
+// Pair p works for group p % 4 on the row ranges p / 4, p / 4 + lanes, ...: the four pairs of a lane walk the same rows;
+// whichever asks for a tile first brings it into L2 and the others mostly find it there.
+__global__ void __launch_bounds__(192, 1)
+k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
+  extern __shared__ __align__(1024) uint8_t oz_raw[];
+  uint8_t* tiles = (uint8_t*)(((uintptr_t)oz_raw + 1023) & ~(uintptr_t)1023);       // [stage][plane slot][64][128]
+  __shared__ __align__(8) uint64_t full[OZ_MAX_STAGES], empty[OZ_MAX_STAGES], acc_full, acc_empty;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = oz_cluster_rank();
+  const int pair = blockIdx.x >> 1;
+  const int group = pair % OZ_GROUPS, lane_id = pair / OZ_GROUPS;
+  const int np = c_oz_nplanes[group];
+  const int nst = OZ_TILES / np;                     // pipeline stages of this group (5 or 6)
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < OZ_MAX_STAGES; s++) { oz_mbar_init(&full[s], 2); oz_mbar_init(&empty[s], 1); }
+
+    oz_mbar_init(&acc_full, 1);
+    oz_mbar_init(&acc_empty, 8);          // four epilogue warps (2..5) of each CTA
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(oz_smem(&tmem_base_s)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  oz_cluster_sync();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int chunks_per_range = a.range_rows / OZ_KC;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ producer (both CTAs): TMA tensor copies
+    if (lane == 0) {
+      const uint32_t lead_full0 = oz_smem(&full[0]) & 0xFEFFFFFFu;      // the leader's copy of the barrier
+      int it = 0, st = 0;
+      unsigned ph = 1;                        // parity that lets the first pass over the ring through
+      for (int range = lane_id; range < a.nranges; range += a.lanes) {
+        const int64_t r0 = (int64_t)range * a.range_rows;
+        int64_t rem = a.n - r0;
+        const int nch = (int)((rem < a.range_rows ? (rem + OZ_KC - 1) / OZ_KC : chunks_per_range));
+        for (int ch = 0; ch < nch; ch++, it++) {
+          oz_mbar_wait(&empty[st], ph);
+          if (rank == 0) oz_mbar_expect_tx(&full[st], 2u * (uint32_t)np * OZ_TILE);
+          else oz_mbar_arrive_remote(&full[st], 0);
+          const uint32_t bar = lead_full0 + (uint32_t)st * 8u;
+          const int c0 = (int)rank * OZ_HALF;
+          const int c1 = (int)(r0 + (int64_t)ch * OZ_KC);
+          for (int q = 0; q < np; q++) {
+            const uint32_t dst = oz_smem(tiles + ((size_t)st * np + q) * OZ_TILE);
+            const int c2 = c_oz_planes[group][q];
+            asm volatile("cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+                         " [%0], [%1, {%3, %4, %5}], [%2];"
+                         :: "r"(dst), "l"(&tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+          }
+          if (++st == nst) { st = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (leader CTA, one thread)
+    if (rank == 0 && lane == 0) {
+      // staged position of every plane of this group
+      int pos[OZ_S];
+      for (int p = 0; p < OZ_S; p++) pos[p] = 0;
+      for (int q = 0; q < np; q++) pos[c_oz_planes[group][q]] = q;
+      int item = 0, st = 0;
+      unsigned ph = 0;
+      for (int range = lane_id; range < a.nranges; range += a.lanes, item++) {
+        const int64_t r0 = (int64_t)range * a.range_rows;
+        int64_t rem = a.n - r0;
+        const int nch = (int)((rem < a.range_rows ? (rem + OZ_KC - 1) / OZ_KC : chunks_per_range));
+        if (item > 0) oz_mbar_wait(&acc_empty, (unsigned)((item - 1) & 1));      // the epilogue has drained the accumulators
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint32_t started = 0;                 // bit s: slot s holds a partial sum of this item
+        for (int ch = 0; ch < nch; ch++) {
+          oz_mbar_wait(&full[st], ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t stage_base = oz_smem(tiles + (size_t)st * np * OZ_TILE);
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            const OzProduct pr = c_oz_products[group][k];
+            if (pr.slot < 0) continue;
+            const uint32_t abase = stage_base + (uint32_t)pos[pr.pa] * OZ_TILE;
+            const uint32_t bbase = stage_base + (uint32_t)pos[pr.pb] * OZ_TILE;
+            const uint32_t dcol = tmem_base + (uint32_t)pr.slot * 256u;
+#pragma unroll
+            for (int ks = 0; ks < OZ_KC / 32; ks++) {
+              const uint64_t ad = oz_desc(abase + ks * 32 * OZ_HALF);
+              const uint64_t bd = oz_desc(bbase + ks * 32 * OZ_HALF);
+              const uint32_t acc = (started >> pr.slot) & 1u;
+              asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                           "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}"
+                           :: "r"(dcol), "l"(ad), "l"(bd), "r"(OZ_IDESC), "r"(acc), "r"(0u) : "memory");
+              started |= 1u << pr.slot;
+            }
+          }
+          // the stage may be refilled (both CTAs) once these MMAs have read it
+          asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                       :: "r"(oz_smem(&empty[st])), "h"((uint16_t)3) : "memory");
+          if (++st == nst) { st = 0; ph ^= 1u; }
+        }
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     :: "r"(oz_smem(&acc_full)), "h"((uint16_t)3) : "memory");
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue warps 2..5 (both CTAs)
+    const int q = warp & 3;                          // lane quarter of tensor memory this warp may read
+    int item = 0;
+    for (int range = lane_id; range < a.nranges; range += a.lanes, item++) {
+      oz_mbar_wait(&acc_full, (unsigned)(item & 1));
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int row = (int)rank * 128 + q * 32 + lane;
+      for (int s = 0; s < OZ_SLOTS; s++) {
+        int32_t* dst = a.part + ((((size_t)range * OZ_GROUPS + group) * OZ_SLOTS + s) * 256 + row) * 256;
+        for (int c0 = 0; c0 < 256; c0 += 32) {
+          uint32_t v[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * 256 + c0);
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                       "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                         "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                         "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                         "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                       : "r"(taddr));
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<uint4*>(dst + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        if (rank == 0) oz_mbar_arrive(&acc_empty);
+        else oz_mbar_arrive_remote(&acc_empty, 0);
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  oz_cluster_sync();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" :: "r"(tmem_base));
+}
+
+// ------------------------------------------------------------------------------------------------ finish
+// step 1: exact sums over the ranges, one thread per accumulator entry (coalesced)
+__global__ void __launch_bounds__(256)
+k_oz_reduce(const int32_t* __restrict__ part, int nranges, long long* __restrict__ sums) {
+  const size_t total = (size_t)OZ_GROUPS * OZ_SLOTS * 65536;
+  for (size_t e = (size_t)blockIdx.x * 256 + threadIdx.x; e < total; e += (size_t)gridDim.x * 256) {
+    long long a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    int r = 0;
+    for (; r + 4 <= nranges; r += 4) {
+      a0 += part[(size_t)r * total + e];
+      a1 += part[(size_t)(r + 1) * total + e];
+      a2 += part[(size_t)(r + 2) * total + e];
+      a3 += part[(size_t)(r + 3) * total + e];
+    }
+    for (; r < nranges; r++) a0 += part[(size_t)r * total + e];
+    sums[e] = (a0 + a1) + (a2 + a3);
+  }
+}
+
+struct OzFinishArgs {
+  int64_t d, ldc;
+  const long long* sums;    // [OZ_GROUPS][OZ_SLOTS][256][256]
+  const OzPrep* prep;
+  int ew;
+  const int* flag;
+  double* out;              // d x d corner, row stride ldc
+};
+
+// step 2: levels, scales, mirror
+__global__ void __launch_bounds__(256)
+k_oz_finish(const OzFinishArgs a) {
+  const int64_t d = a.d;
+  const int64_t nh = d * (d + 1) / 2;
+  const bool poisoned = (*a.flag != 0) || (a.prep->bad != 0);
+  for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < nh; e += (int64_t)gridDim.x * 256) {
+    int64_t i = 0, rem = e;
+    while (rem >= d - i) { rem -= d - i; i++; }
+    const int64_t j = i + rem;
+    long long lev[OZ_LEVELS] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int g = 0; g < OZ_GROUPS; g++)
+#pragma unroll
+      for (int s = 0; s < OZ_SLOTS; s++) {
+        const long long* t = a.sums + ((size_t)g * OZ_SLOTS + s) * 65536;
+        long long v = t[i * 256 + j];
+        if (c_oz_slot_off[g][s]) v += t[j * 256 + i];
+        lev[c_oz_slot_level[g][s]] += v;
+      }
+    // sum_L lev[L] 256^(8-L), smallest terms first; every term is exact in double
+    double acc = 0.0;
+#pragma unroll
+    for (int L = OZ_LEVELS - 1; L >= 0; L--) acc += scalbn((double)lev[L], 8 * (8 - L));
+    const int qi = OZ_VBITS - a.prep->colexp[i] - a.ew, qj = OZ_VBITS - a.prep->colexp[j] - a.ew;
+    double h = (a.prep->colexp[i] == INT32_MIN || a.prep->colexp[j] == INT32_MIN) ? 0.0 : scalbn(scalbn(acc, -qi), -qj);
+    if (poisoned) h = __longlong_as_double(0x7ff8000000000000ll);
+    a.out[i * a.ldc + j] = h;
+    a.out[j * a.ldc + i] = h;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+static inline size_t oz_align(size_t v) { return (v + 1023) & ~(size_t)1023; }
+
+struct OzPlan {
+  int range_rows, nranges, lanes, pairs;
+  int64_t n_alloc;
+  size_t off_planes, off_part, off_sums, off_flag, total;
+};
+
+static OzPlan oz_plan(int device, int64_t n) {
+  OzPlan p;
+  const int sms = dev_info(device).sms;
+  p.pairs = ((sms / 2) / OZ_GROUPS) * OZ_GROUPS;
+  if (p.pairs < OZ_GROUPS) p.pairs = OZ_GROUPS;
+  p.lanes = p.pairs / OZ_GROUPS;
+  int64_t per_lane = (n + p.lanes - 1) / p.lanes;
+  int64_t rr = ((per_lane + OZ_KC - 1) / OZ_KC) * OZ_KC;
+  if (rr < OZ_KC) rr = OZ_KC;
+  if (rr > OZ_MAX_RANGE) rr = OZ_MAX_RANGE;
+  p.range_rows = (int)rr;
+  p.nranges = (int)((n + rr - 1) / rr);
+  if (p.nranges < 1) p.nranges = 1;
+  p.n_alloc = n > 0 ? n : 1;
+  size_t cur = 0;
+  p.off_planes = cur; cur += oz_align((size_t)OZ_S * p.n_alloc * OZ_COLS);
+  p.off_part = cur; cur += oz_align((size_t)p.nranges * OZ_GROUPS * OZ_SLOTS * 65536 * sizeof(int32_t));
+  p.off_sums = cur; cur += oz_align((size_t)OZ_GROUPS * OZ_SLOTS * 65536 * sizeof(long long));
+  p.off_flag = cur; cur += 1024;
+  p.total = cur;
+  return p;
+}
+
+bool oz_applicable(int family, int64_t n, int64_t d, int64_t ldx, const double* x) {
+  if (!(family == NB_GLM_LOGISTIC || family == NB_GLM_LOGISTIC_IRLS || family == NB_GLM_LINEAR)) return false;
+  return n > 0 && d > 128 && d <= 256 && (d % 4 == 0) && (ldx % 4 == 0) && ((((uintptr_t)x) & 31) == 0) &&
+         n < ((int64_t)1 << 31);
+}
+
+size_t oz_scratch_bytes(int device, int64_t n) { return oz_plan(device, n).total; }
+
+typedef CUresult (*OzEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static OzEncodeFn oz_encode_fn() {
+  static OzEncodeFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+        qr == cudaDriverEntryPointSuccess)
+      fn = (OzEncodeFn)p;
+  });
+  return fn;
+}
+
+// pass A + pass B + finish.  `stats` receives g, objective, the intercept row/column of H (through
+// k_glm_rows_finish, launched by the caller's usual path) and the d x d corner of H.
+int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                 const double* beta, int skip_obj, const void* prep, double* stats, double* parts, int max_parts,
+                 int* nparts, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  const OzPlan p = oz_plan(device, n);
+  NB_REQUIRE(scratch != nullptr && scratch_bytes >= p.total, "int8 Hessian: scratch too small (%zu < %zu)",
+             scratch_bytes, p.total);
+  OzEncodeFn enc = oz_encode_fn();
+  NB_REQUIRE(enc != nullptr, "int8 Hessian: cuTensorMapEncodeTiled is not available from this driver");
+  char* sc = (char*)scratch;
+  int8_t* planes = (int8_t*)(sc + p.off_planes);
+  int32_t* part = (int32_t*)(sc + p.off_part);
+  int* flag = (int*)(sc + p.off_flag);
+  const int ew = family == NB_GLM_LINEAR ? 0 : -1;       // sqrt(w) <= 1 (linear), <= 1/2 (logistic: w = mu (1 - mu))
+  NB_CHECK(cudaMemsetAsync(flag, 0, sizeof(int), st));
+
+  OzRowsArgs ra;
+  ra.x = x; ra.n = n; ra.d = d; ra.ldx = ldx; ra.y = y; ra.ydt = ydt; ra.beta = beta; ra.family = family;
+  ra.skip_obj = skip_obj; ra.ew = ew; ra.prep = (const OzPrep*)prep; ra.planes = planes;
+  ra.plane_stride = p.n_alloc * OZ_COLS; ra.partials = parts; ra.flag = flag;
+  int64_t want = ((n + OZ_R - 1) / OZ_R + (OZ_ROWS_THREADS / 32) - 1) / (OZ_ROWS_THREADS / 32);
+  int64_t grid = (int64_t)dev_info(device).sms * 2;
+  static KernelSetup rows_setup;
+  int occ = 1;
+  if (int rc = rows_setup.get(device, k_oz_rows, OZ_ROWS_THREADS, 0, &occ)) return rc;
+  grid = (int64_t)dev_info(device).sms * occ;
+  if (grid > max_parts) grid = max_parts;
+  if (grid > want) grid = want;
+  if (grid < 1) grid = 1;
+  k_oz_rows<<<(unsigned)grid, OZ_ROWS_THREADS, 0, st>>>(ra);
+  NB_LAUNCH_CHECK();
+  *nparts = (int)grid;
+
+  CUtensorMap tm;
+  cuuint64_t dims[3] = {(cuuint64_t)OZ_COLS, (cuuint64_t)n, (cuuint64_t)OZ_S};
+  cuuint64_t strides[2] = {(cuuint64_t)OZ_COLS, (cuuint64_t)p.n_alloc * OZ_COLS};
+  cuuint32_t box[3] = {OZ_HALF, OZ_KC, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult cr = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  NB_REQUIRE(cr == CUDA_SUCCESS, "int8 Hessian: cuTensorMapEncodeTiled failed (%d)", (int)cr);
+
+  OzGemmArgs ga;
+  ga.n = n; ga.range_rows = p.range_rows; ga.nranges = p.nranges; ga.lanes = p.lanes; ga.part = part;
+  const size_t smem = (size_t)OZ_TILES * OZ_TILE + 1024;
+  static bool gemm_ready[NB_MAX_DEVICES] = {};
+  if (device < 0 || device >= NB_MAX_DEVICES || !gemm_ready[device]) {
+    NB_CHECK(cudaFuncSetAttribute(k_oz_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (device >= 0 && device < NB_MAX_DEVICES) gemm_ready[device] = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * p.pairs));
+  cfg.blockDim = dim3(192);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm, tm, ga));
+
+  long long* sums = (long long*)(sc + p.off_sums);
+  k_oz_reduce<<<dev_info(device).sms * 4, 256, 0, st>>>(part, p.nranges, sums);
+  NB_LAUNCH_CHECK();
+  OzFinishArgs fa;
+  fa.d = d; fa.ldc = d + 1; fa.sums = sums; fa.prep = (const OzPrep*)prep; fa.ew = ew;
+  fa.flag = flag; fa.out = stats;
+  const int64_t blocks = (d * (d + 1) / 2 + 255) / 256;
+  k_oz_finish<<<(unsigned)blocks, 256, 0, st>>>(fa);
+  NB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+size_t nb_glm_prep_bytes(int64_t d) {
+  (void)d;
+  return sizeof(OzPrep) + OZ_COLS * sizeof(unsigned long long) + (size_t)OZ_PREP_CTAS * OZ_COLS * sizeof(double);
+}
+
+int nb_glm_prepare(int device, const double* x_d, int64_t n, int64_t d, int64_t ldx, void* prep_d, size_t prep_bytes,
+                   void* stream) {
+  NB_ENTER(device);
+  NB_REQUIRE(d >= 1 && d <= OZ_COLS && n >= 0 && ldx >= d, "nb_glm_prepare: bad shape n=%lld d=%lld ldx=%lld",
+             (long long)n, (long long)d, (long long)ldx);
+  NB_REQUIRE(prep_d != nullptr && prep_bytes >= nb_glm_prep_bytes(d), "nb_glm_prepare: buffer too small");
+  unsigned long long* maxbits = (unsigned long long*)((char*)prep_d + sizeof(OzPrep));
+  double* sumsq = (double*)(maxbits + OZ_COLS);
+  NB_CHECK(cudaMemsetAsync(maxbits, 0, OZ_COLS * sizeof(unsigned long long), st));
+  int64_t grid = OZ_PREP_CTAS;
+  if (grid > n) grid = n;
+  if (n > 0) {
+    k_oz_colmax<<<(unsigned)grid, 256, 0, st>>>(x_d, n, d, ldx, maxbits, sumsq);
+    NB_LAUNCH_CHECK();
+  }
+  k_oz_colexp<<<1, 256, 0, st>>>(maxbits, sumsq, n > 0 ? (int)grid : 0, n, d, (OzPrep*)prep_d);
+  NB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

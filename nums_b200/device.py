@@ -46,10 +46,11 @@ class DeviceBlock:
     Wraps a torch tensor used purely as a typed, strided window on device memory.  Like the
     NumPy blocks of the reference it is immutable by convention (numpy_kernel.py:131-135)."""
 
-    __slots__ = ("t",)
+    __slots__ = ("t", "prep")
 
     def __init__(self, tensor):
         self.t = tensor
+        self.prep = None      # per-block column scales of the int8 Hessian path (fused.glm_prepare), made on first use
 
     # --- metadata (host side only) ---
     @property
@@ -126,7 +127,8 @@ def upload_bytes(data, device_index):
 
 
 def from_numpy(arr, device_index):
-    """Host ndarray / NumPy scalar -> DeviceBlock (H2D copy through pinned staging)."""
+    """Host ndarray / NumPy scalar -> DeviceBlock: copied straight from the caller's buffer in 256 MiB pieces (at the
+    link rate when that buffer is page-locked, through the driver's staging otherwise)."""
     require_cuda()
     arr = np.asarray(arr)
     if arr.dtype == np.dtype(np.int32) or arr.dtype == np.dtype(np.float32):

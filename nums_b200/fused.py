@@ -3,7 +3,10 @@ reference's own fusion uses: nums/experimental/optimizer/graph.py:801-810, invok
 
 Each takes/returns DeviceBlocks and calls one C-ABI entry point of libnumsb200.so.
 """
+import os
+
 import numpy as np
+import torch
 
 from . import _lib
 from . import device as dv
@@ -11,9 +14,59 @@ from . import hostlogic as hl
 from .device import DeviceBlock
 
 
-def glm_stats(x, y, beta, family, want_hess, need_obj=True):
+NB_GLM_INT8_HESSIAN = 4
+_HESSIAN_MODES = ("fp64", "int8", "int8!")
+
+
+def default_hessian():
+    """Which kernel forms X^T diag(w) X for 128 < d <= 256: "int8" (tcgen05 integer tensor path, error-free digit
+    split, csrc/glm_ozaki.cu) or "fp64" (DMMA, csrc/glm_fused.cu).  NUMS_B200_HESSIAN overrides the default."""
+    mode = os.environ.get("NUMS_B200_HESSIAN", "int8")
+    if mode not in _HESSIAN_MODES:
+        raise ValueError("NUMS_B200_HESSIAN must be one of %s" % (_HESSIAN_MODES,))
+    return mode
+
+
+def int8_hessian_applies(x, family):
+    n, d = x.shape
+    return (family in ("logistic", "logistic_irls", "linear") and n > 0 and 128 < d <= 256 and d % 4 == 0
+            and x.strides[1] == 1 and x.strides[0] % 4 == 0 and x.ptr % 32 == 0)
+
+
+INT8_MAX_RANGE_LOG2 = 5     # largest entry of a column at most 32x its r.m.s.: fixed-point error of H below 1e-10
+
+
+class BlockPrep:
+    """What nb_glm_prepare found in an X block: the device buffer the kernels read, and the verdict read back once."""
+
+    __slots__ = ("buf", "bad", "range_log2")
+
+    def __init__(self, buf, bad, range_log2):
+        self.buf, self.bad, self.range_log2 = buf, bad, range_log2
+
+    @property
+    def usable(self):
+        return not self.bad and self.range_log2 <= INT8_MAX_RANGE_LOG2
+
+
+def glm_prepare(x):
+    """Per-column power-of-two scales of an X block for the int8 Hessian (nb_glm_prepare): one pass over the block
+    and one 8-byte read-back, kept with the block (blocks are immutable by convention, numpy_kernel.py:131-135)."""
+    if x.prep is None:
+        lib = _lib.load()
+        dev = x.device_index
+        n, d = x.shape
+        buf = dv.scratch(lib.nb_glm_prep_bytes(d), dev)
+        _lib.check(lib.nb_glm_prepare(dev, x.ptr, n, d, x.strides[0], buf.data_ptr(), buf.numel(), dv.stream_ptr(dev)))
+        verdict = buf[1024:1032].view(torch.int32).cpu()
+        x.prep = BlockPrep(buf, bool(int(verdict[0])), int(verdict[1]))
+    return x.prep
+
+
+def glm_stats(x, y, beta, family, want_hess, need_obj=True, hessian=None):
     """Packed [H (p*p) | g (p) | objective (1)] of one row block (see nb_glm_stats).  need_obj=False (with
-    want_hess) leaves the objective out: the Newton loop never reads it."""
+    want_hess) leaves the objective out: the Newton loop never reads it.  hessian: "int8" | "fp64" | None (default);
+    "int8" falls back to FP64 for a block whose columns have a large dynamic range (BlockPrep.usable)."""
     lib = _lib.load()
     dev = x.device_index
     if x.ndim != 2 or x.dtype != np.dtype(np.float64):
@@ -30,10 +83,18 @@ def glm_stats(x, y, beta, family, want_hess, need_obj=True):
     out = dv.empty((lib.nb_glm_stats_len(d),), np.float64, dev)
     if not want_hess:   # the H part is not written by the kernel: keep the buffer defined for the all-reduce
         _lib.check(lib.nb_fill(dev, out.size, out.ptr, out.code, 0.0, 0, dv.stream_ptr(dev)))
-    sc = dv.scratch(lib.nb_glm_scratch_bytes(dev, n, d, int(bool(want_hess))), dev)
     mode = 3 if (want_hess and not need_obj) else int(bool(want_hess))      # 3 = NB_GLM_HESS_NO_OBJECTIVE
-    _lib.check(lib.nb_glm_stats(dev, hl.FAMILY_CODE[family], x.ptr, n, d, x.strides[0], y.ptr, y.code, beta.ptr,
-                                mode, out.ptr, sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+    prep = None
+    choice = hessian or default_hessian()
+    if want_hess and choice in ("int8", "int8!") and int8_hessian_applies(x, family):
+        found = glm_prepare(x)
+        if found.usable or choice == "int8!":     # "int8!": whatever the dynamic range of the columns (tests)
+            prep = found.buf.data_ptr()
+            mode |= NB_GLM_INT8_HESSIAN
+    sc = dv.scratch(lib.nb_glm_scratch_bytes(dev, n, d, mode), dev)
+    _lib.check(lib.nb_glm_stats_prepared(dev, hl.FAMILY_CODE[family], x.ptr, n, d, x.strides[0], y.ptr, y.code,
+                                         beta.ptr, mode, prep, out.ptr, sc.data_ptr(), sc.numel(),
+                                         dv.stream_ptr(dev)))
     return out
 
 

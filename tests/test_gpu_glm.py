@@ -146,13 +146,20 @@ def test_linear_poisson(app, fused, tag, cls, ykey, kw):
 # ------------------------------------------------------------------------------------------------
 # GLM: seeded comparisons with the oracle across the kernel's column-width configurations
 # ------------------------------------------------------------------------------------------------
-def raw_stats(n, d, family, ydtype, ldx=None, seed=0):
-    """nb_glm_stats through the C ABI on one block -> (H, g, obj) and the oracle's."""
+def raw_stats(n, d, family, ydtype, ldx=None, seed=0, hessian=None, spread=None):
+    """nb_glm_stats through the C ABI on one block -> (H, g, obj) and the oracle's.  spread: per-column scales
+    10^U(-spread, spread) and a few outliers, for the per-column fixed-point scaling of the int8 Hessian."""
     from nums_b200 import device as dv, fused
     from nums_b200.device import DeviceBlock
     rng = np.random.default_rng(seed + d)
     X = rng.standard_normal((n, d)) / np.sqrt(d)
     beta = rng.standard_normal(d + 1) * 0.5
+    if spread is not None:
+        scale = 10.0 ** rng.uniform(-spread, spread, d)
+        X = X * scale
+        X[rng.integers(0, n, 20), rng.integers(0, d, 20)] *= 50.0        # outliers set the column scale
+        X[:, 3] = 0.0                                                     # an all-zero column
+        beta[:d] = beta[:d] / scale
     if family == "logistic":
         y = (rng.random(n) < 0.4).astype(ydtype)
     elif family == "poisson":
@@ -165,7 +172,7 @@ def raw_stats(n, d, family, ydtype, ldx=None, seed=0):
         wide = np.zeros((n, ldx))
         wide[:, :d] = X
         Xd = DeviceBlock(dv.from_numpy(wide, 0).t[:, :d])
-    s = dv.to_numpy(fused.glm_stats(Xd, dv.from_numpy(y, 0), dv.from_numpy(beta, 0), family, True))
+    s = dv.to_numpy(fused.glm_stats(Xd, dv.from_numpy(y, 0), dv.from_numpy(beta, 0), family, True, hessian=hessian))
     p = d + 1
     model = oglm.BlockedGLM(family, [X], [y])
     fwd = model.forward(beta)
@@ -182,6 +189,68 @@ def test_glm_stats_vs_oracle_logistic(app, n, d):
     assert rel_err(H, H0) < STAT_TOL
     assert rel_err(obj, obj0) < STAT_TOL
     assert np.array_equal(H, H.T)
+
+
+@pytest.mark.parametrize("hessian", ["int8!", "int8", "fp64"])
+@pytest.mark.parametrize("family", ["logistic", "linear"])
+@pytest.mark.parametrize("n,d,ldx,spread", [(40_000, 256, None, None), (1_153, 256, None, None), (63, 256, None, None),
+                                            (20_001, 132, None, None), (70_007, 200, 204, None),
+                                            (30_000, 256, None, 3.0), (2_400_000, 256, None, None)])
+def test_hessian_int8_tensor_path_and_fp64_path(app, hessian, family, n, d, ldx, spread):
+    """X^T diag(w) X for 128 < d <= 256 on the integer tensor path (tcgen05 kind::i8, csrc/glm_ozaki.cu) and on the
+    FP64 DMMA path, both against the oracle at the same bar: ragged row counts, a row count below one pipeline stage,
+    several accumulation ranges per pair (2.4e6 rows), a strided block, columns of very different scale with outliers
+    and an all-zero column.  "int8!" forces the integer path; "int8" (the default) is the integer path unless
+    nb_glm_prepare finds columns whose largest entries stand far above their r.m.s. (fused.BlockPrep.usable): the
+    39-bit fixed point then loses those leading bits, and the block goes to FP64."""
+    if n > 1_000_000 and (family == "linear" or hessian == "int8"):
+        pytest.skip("one large case is enough")
+    ydtype = np.int64 if family == "logistic" else np.float64
+    (H, g, obj), (H0, g0, obj0) = raw_stats(n, d, family, ydtype, ldx, seed=11, hessian=hessian, spread=spread)
+    assert rel_err(g, g0) < STAT_TOL and rel_err(obj, obj0) < STAT_TOL
+    assert np.array_equal(H, H.T)
+    if spread is None:
+        assert rel_err(H, H0) < STAT_TOL
+    else:
+        # columns differ by orders of magnitude: compare every entry against the scale of its row and column
+        s = np.sqrt(np.maximum(np.diag(H0), 1e-300))
+        scaled = np.max(np.abs(H - H0) / np.outer(s, s))
+        # forced onto the integer path, outliers 50-150x the r.m.s. of their column cost 6-7 of the 39 bits: the
+        # stated bound 2^-38 * max/rms holds; the default ("int8") has sent this block to FP64
+        assert scaled < (5e-9 if hessian == "int8!" else STAT_TOL)
+        assert rel_err(H, H0) < STAT_TOL
+        assert np.all(H[3, :-1] == 0.0) and np.all(H[:-1, 3] == 0.0)
+
+
+def test_hessian_int8_rejects_a_foreign_column_scale(app):
+    """The digit split relies on the block's own column maxima.  Handing the kernel the scales of another block
+    (values up to 1000x larger than prepared for) must not give a plausible Hessian: H comes back NaN."""
+    from nums_b200 import device as dv, fused
+    rng = np.random.default_rng(5)
+    n, d = 5000, 256
+    small = dv.from_numpy(rng.standard_normal((n, d)) * 1e-3, 0)
+    big = dv.from_numpy(rng.standard_normal((n, d)), 0)
+    big.prep = fused.glm_prepare(small)
+    y = dv.from_numpy((rng.random(n) < 0.5).astype(np.int64), 0)
+    s = dv.to_numpy(fused.glm_stats(big, y, dv.from_numpy(np.zeros(d + 1), 0), "logistic", True, hessian="int8"))
+    p = d + 1
+    assert np.all(np.isnan(s[: p * p].reshape(p, p)[:d, :d]))
+    assert np.all(np.isfinite(s[p * p:]))
+
+
+def test_hessian_int8_verdict_of_prepare(app):
+    """nb_glm_prepare's read-back: Gaussian columns are usable (largest entry ~5 r.m.s.), a column with one entry at
+    1000 r.m.s. is not, Inf is flagged."""
+    from nums_b200 import device as dv, fused
+    rng = np.random.default_rng(6)
+    X = rng.standard_normal((20000, 132))
+    a = fused.glm_prepare(dv.from_numpy(X, 0))
+    assert a.usable and not a.bad and 2 <= a.range_log2 <= 3
+    X2 = X.copy(); X2[17, 5] = 1000.0
+    b = fused.glm_prepare(dv.from_numpy(X2, 0))
+    assert not b.usable and b.range_log2 == 8        # 1000 against an r.m.s. of 7.1 (the outlier raises it)
+    X3 = X.copy(); X3[3, 3] = np.inf
+    assert fused.glm_prepare(dv.from_numpy(X3, 0)).bad
 
 
 @pytest.mark.parametrize("family,ydtype", [("linear", np.float64), ("poisson", np.int64), ("poisson", np.float64)])
