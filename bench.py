@@ -10,8 +10,15 @@ not fit one 180 GB GPU, so N=1 runs the per-GPU shard.  A "step" is one Newton i
 (nums/models/glms.py:660-676): fused statistics pass over the shard, one all-reduce of the packed
 p*p+p+1 doubles, the replicated Newton update, and the 8-byte convergence read-back.
 metric = algorithmic HBM bytes of the pass, n*(8d+8) summed over ranks, per second.
+
+Besides the headline the line carries, measured in the same run: the kernels of the step timed apart
+(`roofline`, `tensor`, `fp64`), the other BASELINE configurations (`extras`: configs 2, 3, 5 at their own
+sizes), at N > 1 a parity check of the sharded fit against the same rows on one rank (`parity_multi`) and
+the real 10^8 x 256 array split N ways (`strong`), the end-to-end fit from host buffers (`e2e`) and the
+reference's own CPU implementation on a bounded sample (`cpu_baseline`).
 """
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -30,6 +37,7 @@ D_DEFAULT = 256
 ROWS_DEFAULT = 12_500_000
 CHUNK_ROWS = 1 << 19          # rows drawn from the reference's block RNG, then tiled over the shard
 L2_NOTE = "inputs (25.6 GB/GPU) far exceed the 126 MB L2; no flush needed"
+INT8_TOPS_NOMINAL = 4500.0    # dense int8 tensor peak of a B200 (no measured int8 figure in MEASURED_PEAKS.json)
 
 
 def parse():
@@ -41,9 +49,11 @@ def parse():
     ap.add_argument("--rows", type=int, default=ROWS_DEFAULT, help="rows per GPU (weak scaling)")
     ap.add_argument("--d", type=int, default=D_DEFAULT)
     ap.add_argument("--cpu-rows", type=int, default=400_000, help="rows of the bounded CPU-baseline sample")
-    ap.add_argument("--cpu-steps", type=int, default=5)
+    ap.add_argument("--cpu-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--no-strong", action="store_true")
     return ap.parse_args()
 
 
@@ -61,50 +71,76 @@ def algorithmic_bytes(n, d):
     return n * (8 * d + 8)
 
 
+def host_threads():
+    import psutil
+    cores = psutil.cpu_count(logical=False) or os.cpu_count() or 1
+    return max(1, min(cores, len(os.sched_getaffinity(0))))
+
+
 # ------------------------------------------------------------------------------------------------
-# reference arm / CPU baseline: the oracle port of the reference algorithm on the host cores
+# reference arm / CPU baseline: the reference's own code (oracle/_ref) on the host cores, else the oracle port
 # ------------------------------------------------------------------------------------------------
 def cpu_newton_steps(rows, d, steps, warmup=1):
-    """Times `steps` Newton iterations of the reference algorithm (oracle/glm.py: per-block NumPy calls
-    incl. the materialised s*X) on a bounded sample.  Returns (GB/s, seconds per step, threads)."""
-    from oracle import glm as oglm
+    """Times `steps` Newton iterations of the reference on a bounded sample: the unmodified nums package
+    (oracle/_ref: nums.models.glms.LogisticRegression on its SerialBackend, NumPy/OpenBLAS kernels) when it travelled
+    with the repository, else the oracle port of the same algorithm.  Returns (GB/s, s/step, threads, kind)."""
     try:
         from threadpoolctl import threadpool_limits
     except Exception:  # pragma: no cover
         threadpool_limits = None
-    import psutil
-    cores = psutil.cpu_count(logical=False) or os.cpu_count() or 1
-    cores = max(1, min(cores, len(os.sched_getaffinity(0))))
+    cores = host_threads()
     X, y = host_chunk(0, rows, d)
-    model = oglm.BlockedGLM("logistic", oglm.split_rows(X, max(1, rows // 4)), oglm.split_rows(y, max(1, rows // 4)),
-                            "l2", 0.1)
+    from oracle import refharness
+    if refharness.present():
+        import io
+        import warnings
+        warnings.simplefilter("ignore")
+        app = refharness.use(refharness.serial_app(1))
+        from nums.models.glms import LogisticRegression
+        rb = max(1, rows // 4)
+        Xb, yb = app.array(X, block_shape=(rb, d)), app.array(y, block_shape=(rb,))
 
-    def run(k):
-        beta = np.zeros(d + 1)
-        for _ in range(k):
-            fwd = model.forward(beta)
-            g = model.gradient(beta, fwd)
-            H = model.hessian(beta, fwd)
-            beta = beta - np.linalg.inv(H) @ g
-            float(np.max(np.abs(g)))
-        return beta
+        def run(k):
+            m = LogisticRegression(solver="newton", penalty="l2", C=10, tol=-1.0, max_iter=k)
+            with contextlib.redirect_stdout(io.StringIO()):
+                m.fit(Xb, yb)
+            return m._beta.get()
+        kind = "reference"
+    else:
+        from oracle import glm as oglm
+        model = oglm.BlockedGLM("logistic", oglm.split_rows(X, max(1, rows // 4)), oglm.split_rows(y, max(1, rows // 4)),
+                                "l2", 0.1)
 
-    import contextlib
+        def run(k):
+            beta = np.zeros(d + 1)
+            for _ in range(k):
+                fwd = model.forward(beta)
+                g = model.gradient(beta, fwd)
+                H = model.hessian(beta, fwd)
+                beta = beta - np.linalg.inv(H) @ g
+                float(np.max(np.abs(g)))
+            return beta
+        kind = "port"
     with (threadpool_limits(limits=cores) if threadpool_limits else contextlib.nullcontext()):
         run(warmup)
         t0 = time.perf_counter()
         run(steps)
         dt = (time.perf_counter() - t0) / steps
-    return algorithmic_bytes(rows, d) / dt / 1e9, dt, cores
+    return algorithmic_bytes(rows, d) / dt / 1e9, dt, cores, kind
+
+
+def cpu_sample_text(rows, d, steps, cores, kind, dt):
+    what = ("the unmodified reference (oracle/_ref: nums.models.glms.LogisticRegression.fit on SerialBackend, NumPy/OpenBLAS)"
+            if kind == "reference" else "the oracle port of the reference algorithm (oracle/glm.py, NumPy/OpenBLAS)")
+    return "%d x %d float64 rows (4 row blocks), %d Newton iterations of %s on %d threads, %.2f s/iteration" % (
+        rows, d, steps, what, cores, dt)
 
 
 def run_reference(args, result):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    gbs, dt, cores = cpu_newton_steps(args.cpu_rows, args.d, args.steps, max(1, min(args.warmup, 2)))
-    sample = "%d x %d float64 rows (4 row blocks), %d Newton iterations, NumPy/OpenBLAS on %d threads" % (
-        args.cpu_rows, args.d, args.steps, cores)
+    gbs, dt, cores, kind = cpu_newton_steps(args.cpu_rows, args.d, args.steps, max(1, min(args.warmup, 2)))
     line = {
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -112,7 +148,8 @@ def run_reference(args, result):
         "config": {"workload": "LogisticRegression newton, tall-skinny %dx%d float64 per GPU (BASELINE configs[3])"
                                % (args.rows, args.d),
                    "rows_per_gpu": args.rows, "d": args.d, "penalty": "l2", "C": 10},
-        "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": cpu_sample_text(args.cpu_rows, args.d, args.steps, cores, kind, dt)},
         "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -164,9 +201,150 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.rows)}
 
 
+def event_ms(torch, fn, reps, warm=2):
+    """Mean device time of fn() over `reps` calls, CUDA events on the current stream (the one the library launches on)."""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
+def tiled_shard(dv, K_, rank, n, d, local):
+    """Resident synthetic shard: a chunk of the reference's block-RNG stream tiled over n rows (scaled per tile)."""
+    chunk_rows = min(CHUNK_ROWS, n)
+    Xc, yc = host_chunk(rank, chunk_rows, d)
+    X = dv.empty((n, d), np.float64, local)
+    y = dv.empty((n,), np.int64, local)
+    Xc_d, yc_d = dv.from_numpy(Xc, local), dv.from_numpy(yc, local)
+    for t, lo in enumerate(range(0, n, chunk_rows)):
+        hi = min(n, lo + chunk_rows)
+        scaled = K_.bop("mul", Xc_d, dv.from_numpy(np.float64(1.0 + 1e-3 * (t % 7)), local), False, False, {})
+        dv.copy_into(X.t[lo:hi], scaled.t[: hi - lo])
+        dv.copy_into(y.t[lo:hi], yc_d.t[: hi - lo])
+    return X, y, Xc, yc
+
+
+def parity_multi(app, dist, world, rank, local, d):
+    """Sharded fit against the same rows on one rank: 100000*world x d rows drawn per rank from the block RNG, fitted
+    (a) row-sharded with the NCCL all-reduce of the packed statistics, (b) gathered on every rank and fitted without
+    the collective.  Returns max |beta_a - beta_b| and whether the iteration counts agree."""
+    import torch
+    from nums_b200 import device as dv
+    from nums_b200.glms import LogisticRegression
+    rows = 100_000
+    Xs, ys = host_chunk(100 + rank, rows, d)
+    Xd, yd = dv.from_numpy(Xs, local), dv.from_numpy(ys, local)
+    from nums_b200.blockarray import BlockArray
+    from nums_b200.grid import ArrayGrid
+    km = app.km
+    m = LogisticRegression(app=app, solver="newton", penalty="l2", C=10)
+    m.fit(BlockArray.from_oid(Xd, (rows, d), np.float64, km), BlockArray.from_oid(yd, (rows,), np.int64, km))
+    sharded = m._beta_full.get()
+    it_sharded = m.n_iter_
+    allX = [torch.empty_like(Xd.t) for _ in range(world)]
+    ally = [torch.empty_like(yd.t) for _ in range(world)]
+    dist.all_gather(allX, Xd.t)
+    dist.all_gather(ally, yd.t)
+    m2 = LogisticRegression(app=app, solver="newton", penalty="l2", C=10, sharded=False)
+    Xall = BlockArray(ArrayGrid((rows * world, d), (rows, d), "float64"), km)
+    yall = BlockArray(ArrayGrid((rows * world,), (rows,), "int64"), km)
+    for r in range(world):
+        Xall.blocks[(r, 0)].oid = dv.DeviceBlock(allX[r])
+        yall.blocks[(r,)].oid = dv.DeviceBlock(ally[r])
+    m2.fit(Xall, yall)
+    single = m2._beta_full.get()
+    err = float(np.max(np.abs(sharded - single)))
+    t = torch.tensor([err], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return {"rows": rows * world, "d": d, "max_abs_dbeta": float(t.item()), "iters_sharded": it_sharded,
+            "iters_single": m2.n_iter_, "iters_equal": it_sharded == m2.n_iter_,
+            "what": "LogisticRegression newton (l2, C=10) to convergence: row-sharded over %d ranks with the NCCL "
+                    "all-reduce vs the same %d rows as %d blocks on every rank without it" % (world, rows * world, world)}
+
+
+def extras_single_gpu(torch, app, dv, fused, lib, _lib, local, hbm_peak, fp64_peak):
+    """BASELINE configs 2, 3 and 5 at their own sizes on one GPU (device-timed, CUDA events)."""
+    K_ = __import__("nums_b200.cuda_kernel", fromlist=["KernelCls"]).KernelCls()
+    out = {}
+    n = 10 ** 8
+    # ---- config 2: x.T @ x, where(p == c), argmax(p), sum(p) on 10^8 elements
+    x = K_.random_block((1337, 0), "random", (n,), (n,), np.float64, device_index=local)
+    p = K_.permutation((1337, 1), n, device_index=local)
+    ms = event_ms(torch, lambda: K_.bop("tensordot", x, x, True, False, 1), 10)
+    out["dot_1e8"] = {"ms": ms, "gbs": 8 * n / ms / 1e6, "frac_hbm": 8 * n / ms / 1e6 / hbm_peak}
+    c = dv.from_numpy(np.int64(n // 2), local)
+
+    def where_eq():
+        m = K_.bop("eq", p, c, False, False, {})
+        return K_.where(m, None, None, [(0, n)])
+    ms = event_ms(torch, where_eq, 10)
+    out["where_eq_1e8"] = {"ms": ms, "gbs": (8 * n + 2 * n) / ms / 1e6, "frac_hbm": (8 * n + 2 * n) / ms / 1e6 / hbm_peak,
+                           "what": "p == c (8n read, n written) then where (n read twice): 10n bytes"}
+    ms = event_ms(torch, lambda: K_.arg_op("argmax", p, slice(0, n)), 10)
+    out["argmax_1e8"] = {"ms": ms, "gbs": 8 * n / ms / 1e6, "frac_hbm": 8 * n / ms / 1e6 / hbm_peak}
+    ms = event_ms(torch, lambda: K_.reduce_axis("sum", p, None, False, False), 10)
+    out["sum_1e8"] = {"ms": ms, "gbs": 8 * n / ms / 1e6, "frac_hbm": 8 * n / ms / 1e6 / hbm_peak}
+    del x, p
+    torch.cuda.empty_cache()
+    # ---- config 3: 10^4 x 10^4 @ 10^4 x 10^4 float64
+    m = 10 ** 4
+    A = K_.random_block((1337, 2), "random", (m * m,), (m, m), np.float64, device_index=local)
+    B = K_.random_block((1337, 3), "random", (m * m,), (m, m), np.float64, device_index=local)
+    for tag, tb in (("nn", False), ("nt", True)):
+        ms = event_ms(torch, lambda: K_.bop("tensordot", A, B, False, tb, 1), 3, warm=1)
+        tf = 2.0 * m ** 3 / ms / 1e9
+        out["gemm_1e4_" + tag] = {"ms": ms, "tflops": tf, "frac_dmma": (tf / fp64_peak) if fp64_peak else None}
+    del A, B
+    torch.cuda.empty_cache()
+    # ---- config 5: the L-BFGS evaluation (gradient + objective pass) on a 1.25e7 x 1024 shard (102.4 GB)
+    n5, d5 = 12_500_000, 1024
+    free, _ = torch.cuda.mem_get_info()
+    if free > n5 * d5 * 8 + (8 << 30):
+        base = dv.from_numpy(np.random.default_rng(0).standard_normal(1 << 22), local)
+        X5 = dv.empty((n5 * d5,), np.float64, local)
+        for lo in range(0, n5 * d5, base.size):
+            hi = min(n5 * d5, lo + base.size)
+            dv.copy_into(X5.t[lo:hi], base.t[: hi - lo])
+        X5 = dv.DeviceBlock(X5.t.view(n5, d5))
+        y5 = dv.from_numpy(np.random.default_rng(1).poisson(1.0, n5).astype(np.float64), local)
+        b5 = dv.from_numpy(np.random.default_rng(2).standard_normal(d5 + 1) * 1e-3, local)
+        for fam in ("linear", "poisson"):
+            ms = event_ms(torch, lambda: fused.glm_stats(X5, y5, b5, fam, False), 3, warm=1)
+            out["lbfgs_pass_1024_" + fam] = {"rows": n5, "d": d5, "ms": ms, "gbs": n5 * (8 * d5 + 8) / ms / 1e6,
+                                            "frac_hbm": n5 * (8 * d5 + 8) / ms / 1e6 / hbm_peak}
+        del X5, y5, b5
+        torch.cuda.empty_cache()
+    else:
+        out["lbfgs_pass_1024"] = {"skipped": "not enough free HBM (%d GB)" % (free >> 30)}
+    # ---- config 1: README fit (10^6 x 2) wall time
+    from nums_b200.glms import LogisticRegression
+    Xr = np.random.default_rng(3).standard_normal((10 ** 6, 2))
+    Xr[500_000:] += 2.0
+    yr = np.concatenate([np.zeros(500_000, dtype=np.int64), np.ones(500_000, dtype=np.int64)])
+    Xb, yb = app.array(Xr, block_shape=(500_000, 2)), app.array(yr, block_shape=(500_000,))
+
+    def readme():
+        mm = LogisticRegression(app=app, solver="newton", penalty="l2", C=10)
+        mm.fit(Xb, yb)
+        return mm
+    readme()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    mm = readme()
+    torch.cuda.synchronize()
+    out["readme_fit_ms"] = {"ms": (time.perf_counter() - t0) * 1e3, "iterations": mm.n_iter_}
+    return out
+
+
 def run_ours(args, result):
     import torch
     import torch.distributed as dist
@@ -189,29 +367,33 @@ def run_ours(args, result):
     lib = _lib.load()
     n, d, p = args.rows, args.d, args.d + 1
     K, W = args.steps, max(args.warmup, 3)
-
-    # ---- synthetic shard, resident in HBM: reference-RNG chunk tiled over the shard
-    chunk_rows = min(CHUNK_ROWS, n)
-    Xc, yc = host_chunk(rank, chunk_rows, d)
-    X = dv.empty((n, d), np.float64, local)
-    y = dv.empty((n,), np.int64, local)
-    Xc_d, yc_d = dv.from_numpy(Xc, local), dv.from_numpy(yc, local)
     K_ = __import__("nums_b200.cuda_kernel", fromlist=["KernelCls"]).KernelCls()
-    for t, lo in enumerate(range(0, n, chunk_rows)):
-        hi = min(n, lo + chunk_rows)
-        scaled = K_.bop("mul", Xc_d, dv.from_numpy(np.float64(1.0 + 1e-3 * (t % 7)), local), False, False, {})
-        dv.copy_into(X.t[lo:hi], scaled.t[: hi - lo])
-        dv.copy_into(y.t[lo:hi], yc_d.t[: hi - lo])
-    del Xc_d, yc_d
-    Xb = BlockArray.from_oid(X, (n, d), np.float64, km)
-    yb = BlockArray.from_oid(y, (n,), np.int64, km)
-    model = LogisticRegression(app=app, solver="newton", penalty="l2", C=10, tol=-1.0, max_iter=K)
-    model._setup_penalties(p, p)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # ---- N > 1: the sharded fit must give the single-rank coefficients before anything is timed
+    pm = None
+    if world > 1:
+        pm = parity_multi(app, dist, world, rank, local, d)
+        if pm["max_abs_dbeta"] > 1e-8 or not pm["iters_equal"]:
+            if rank == 0:
+                sys.stderr.write("parity_multi FAILED: %s\n" % json.dumps(pm))
+            dist.destroy_process_group()
+            return 4
+
+    # ---- synthetic shard, resident in HBM: reference-RNG chunk tiled over the shard
+    X, y, Xc, yc = tiled_shard(dv, K_, rank, n, d, local)
+    chunk_rows = Xc.shape[0]
+    Xb = BlockArray.from_oid(X, (n, d), np.float64, km)
+    yb = BlockArray.from_oid(y, (n,), np.int64, km)
+    hessian_mode = fused.default_hessian()
+    prep = fused.glm_prepare(X) if fused.int8_hessian_applies(X, "logistic") else None
+    int8_used = bool(prep is not None and prep.usable and hessian_mode == "int8")
+    model = LogisticRegression(app=app, solver="newton", penalty="l2", C=10, tol=-1.0, max_iter=K)
+    model._setup_penalties(p, p)
 
     def newton_steps(k):
         beta = app.zeros((p,), (p,), np.float64)
@@ -246,63 +428,102 @@ def run_ours(args, result):
     fit_sec = time.perf_counter() - t_fit
     fit_iters = fit_model.n_iter_
 
-    # ---- the statistics pass alone (pass 1 + pass 2 + their finish kernels) through the C ABI, timed with
-    # CUDA events on the stream it is launched on; pass 1 alone is timed below, pass 2 is the difference
+    # ---- the kernels of one step, timed apart through the C ABI with CUDA events on the launching stream
     st = dv.stream_ptr(local)
     beta_d = dv.from_numpy(np.full(p, 0.01), local)
     stats_d = dv.empty((lib.nb_glm_stats_len(d),), np.float64, local)
-    sc = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 1), local)
-
-    def gram():
-        _lib.check(lib.nb_glm_stats(local, 1, X.ptr, n, d, d, y.ptr, y.code, beta_d.ptr, 3, stats_d.ptr,
-                                    sc.data_ptr(), sc.numel(), st))
-
-    for _ in range(3):
-        gram()
-    torch.cuda.synchronize()
     reps = max(3, min(K, 10))
-    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    g0.record()
-    for _ in range(reps):
-        gram()
-    g1.record()
-    torch.cuda.synchronize()
-    gram_ms = g0.elapsed_time(g1) / reps
-    # ---- the dominant kernel alone: pass 2 (k_tri_gram + its finish) through nb_matmul_f64, which routes the
-    # symmetric X^T diag(w) X to the same kernel nb_glm_stats uses
+    parts = {}
+
+    def stats_call(mode, prep_ptr, scratch):
+        _lib.check(lib.nb_glm_stats_prepared(local, 1, X.ptr, n, d, d, y.ptr, y.code, beta_d.ptr, mode, prep_ptr,
+                                             stats_d.ptr, scratch.data_ptr(), scratch.numel(), st))
+
+    if int8_used:
+        INT8, ROWS, PROD = fused.NB_GLM_INT8_HESSIAN, 8, 16
+        sc8 = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 3 | INT8), local)
+        pp = prep.buf.data_ptr()
+        parts["stats_int8_ms"] = event_ms(torch, lambda: stats_call(3 | INT8, pp, sc8), reps)
+        parts["rows_ms"] = event_ms(torch, lambda: stats_call(3 | INT8 | ROWS, pp, sc8), reps)
+        parts["products_ms"] = event_ms(torch, lambda: stats_call(3 | INT8 | PROD, pp, sc8), reps)
+        del sc8
+        torch.cuda.empty_cache()
+    sc64 = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 3), local)
+    parts["stats_fp64_ms"] = event_ms(torch, lambda: stats_call(3, None, sc64), 3, warm=1)
+    del sc64
+    # the FP64 Hessian kernel alone (k_tri_gram + its finish) through nb_matmul_f64, which routes the symmetric
+    # X^T diag(w) X to the kernel nb_glm_stats uses
     wbuf = dv.empty((n,), np.float64, local)
     _lib.check(lib.nb_fill(local, n, wbuf.ptr, wbuf.code, 0.25, 0, st))
     Gm = dv.empty((d, d), np.float64, local)
     sc2 = dv.scratch(lib.nb_matmul_scratch_bytes(local, d, d, n), local)
-
-    def tri():
-        _lib.check(lib.nb_matmul_f64(local, d, d, n, X.ptr, 1, d, X.ptr, d, 1, wbuf.ptr, Gm.ptr, d,
-                                     sc2.data_ptr(), sc2.numel(), st))
-
-    for _ in range(3):
-        tri()
-    torch.cuda.synchronize()
-    t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0e.record()
-    for _ in range(reps):
-        tri()
-    t1e.record()
-    torch.cuda.synchronize()
-    tri_ms = t0e.elapsed_time(t1e) / reps
+    tri_ms = event_ms(torch, lambda: _lib.check(lib.nb_matmul_f64(local, d, d, n, X.ptr, 1, d, X.ptr, d, 1, wbuf.ptr, Gm.ptr,
+                                                                   d, sc2.data_ptr(), sc2.numel(), st)), 3, warm=1)
     del wbuf, Gm, sc2
-    # pass 1 alone (HBM-bound link / gradient pass = the L-BFGS evaluation)
-    for _ in range(2):
-        fused.glm_stats(X, y, beta_d, "logistic", False)
-    torch.cuda.synchronize()
-    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    r0.record()
-    for _ in range(reps):
-        fused.glm_stats(X, y, beta_d, "logistic", False)
-    r1.record()
-    torch.cuda.synchronize()
-    rows_ms = r0.elapsed_time(r1) / reps
+    # the gradient / objective pass (what an L-BFGS evaluation runs)
+    grad_ms = event_ms(torch, lambda: fused.glm_stats(X, y, beta_d, "logistic", False), reps)
+    prep_ms = None
+    if prep is not None:
+        def redo_prep():
+            X.prep = None
+            fused.glm_prepare(X)
+        prep_ms = event_ms(torch, redo_prep, 3, warm=1)
     clocks = sampler.stop() if rank == 0 else None
-    del stats_d, sc
+    del stats_d
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    fp64_peak = None
+    try:
+        fp64_peak = json.load(open(os.path.join(ROOT, "profiles", "fp64_peak.json"))).get("dmma_tflops")
+    except Exception:
+        pass
+
+    # ---- N >= 2: the real 10^8 x 256 array split N ways (strong scaling of BASELINE configs[3])
+    strong = None
+    if world > 1 and not args.no_strong:
+        total_rows = 10 ** 8
+        rows_s = total_rows // world
+        if rows_s == n:
+            strong = {"rows_total": total_rows, "rows_per_gpu": rows_s, "ms_per_step": ms_step, "fit_sec": fit_sec,
+                      "fit_iterations": fit_iters, "note": "at this rank count the weak-scaling shard IS 10^8 x 256 / N"}
+        else:
+            del Xb, yb
+            X = y = None
+            torch.cuda.empty_cache()
+            free, _ = torch.cuda.mem_get_info()
+            need = rows_s * d * 8 * (1.0 + 5.0 / 8.0) + (6 << 30)
+            mode_s = "int8" if free > need else "fp64"
+            os.environ["NUMS_B200_HESSIAN"] = mode_s
+            X, y, _, _ = tiled_shard(dv, K_, rank, rows_s, d, local)
+            Xb = BlockArray.from_oid(X, (rows_s, d), np.float64, km)
+            yb = BlockArray.from_oid(y, (rows_s,), np.int64, km)
+            ms_model = LogisticRegression(app=app, solver="newton", penalty="l2", C=10, tol=-1.0, max_iter=5)
+            ms_model._setup_penalties(p, p)
+            newton(ms_model, app.zeros((p,), (p,), np.float64), Xb, yb, -1.0, 2)
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            newton(ms_model, app.zeros((p,), (p,), np.float64), Xb, yb, -1.0, 5)
+            s1.record()
+            barrier()
+            tt = torch.tensor([s0.elapsed_time(s1) / 5], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            fm = LogisticRegression(app=app, solver="newton", penalty="l2", C=10)
+            fm._setup_penalties(p, p)
+            barrier()
+            t0 = time.perf_counter()
+            newton(fm, app.zeros((p,), (p,), np.float64), Xb, yb, fm._tol, fm._max_iter)
+            torch.cuda.synchronize()
+            strong = {"rows_total": total_rows, "rows_per_gpu": rows_s, "hessian": mode_s, "ms_per_step": float(tt.item()),
+                      "gbs": total_rows * (8 * d + 8) / float(tt.item()) / 1e6, "fit_sec": time.perf_counter() - t0,
+                      "fit_iterations": fm.n_iter_}
+            os.environ["NUMS_B200_HESSIAN"] = hessian_mode
 
     # ---- end to end through the public API with HOST buffers (upload + K iterations + read-back)
     e2e = None
@@ -311,7 +532,7 @@ def run_ours(args, result):
         avail = psutil.virtual_memory().available
         per_rank_budget = avail // (3 * max(1, world))
         e_rows = int(min(n, max(chunk_rows, per_rank_budget // (8 * d + 8))))
-        del Xb, yb
+        Xb = yb = None
         X = y = None
         torch.cuda.empty_cache()
         try:
@@ -346,34 +567,69 @@ def run_ours(args, result):
                "rows_per_gpu": e_rows, "seconds": dt,
                "what": "LogisticRegression.fit(host X, host y): upload from pinned host memory + %d Newton "
                        "iterations + coefficient read-back, per rank" % K}
+        del Xh, yh
+
+    extras = None
+    if world == 1 and not args.no_extras:
+        Xb = yb = None
+        X = y = None
+        torch.cuda.empty_cache()
+        extras = extras_single_gpu(torch, app, dv, fused, lib, _lib, local, hbm_peak, fp64_peak)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return 0
 
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    gram_bytes = n * (8 * d + 8)
-    gram_flops_sym = n * d * (d + 1)
-    fp64_peak = None
-    try:
-        fp64_peak = json.load(open(os.path.join(ROOT, "profiles", "fp64_peak.json"))).get("dmma_tflops")
-    except Exception:
-        pass
-    traffic = None       # dram__bytes_read.sum + dram__bytes_write.sum of one k_tri_gram launch (ncu --set full)
+    gram_bytes = algorithmic_bytes(n, d)
+    traffic = {}
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
         if int(tr.get("rows", -1)) == n and int(tr.get("d", -1)) == d:
-            traffic = tr.get("k_tri_gram_dram_bytes")
+            traffic = tr
     except Exception:
         pass
-    executed_flops = 2.0 * n * 1024 * (((d + 31) // 32) * ((d + 31) // 32 + 1) // 2)
+    nblk = (d + 31) // 32
+    # tile products k_tri_gram executes per 4-row step: 16 per off-diagonal 32x32 block, 10 per diagonal block
+    # (its lower 8x8 tiles are skipped), 2 * 8 * 8 * 4 flops each
+    executed_flops = n * 128.0 * (16 * (nblk * (nblk - 1) // 2) + 10 * nblk)
+    useful_flops = float(n) * d * (d + 1)
+    if int8_used:
+        dominant = "rows" if parts["rows_ms"] >= parts["products_ms"] else "products"
+        roof_ms = parts["rows_ms"]
+        roofline = {
+            "bound": "hbm",
+            "kernel": "k_oz_rows (pass A of the int8 Hessian: link, gradient, u and the five int8 digit planes; reads X "
+                      "once, writes 5 bytes per element) + k_glm_rows_finish, timed alone (NB_GLM_INT8_ROWS_ONLY) with CUDA "
+                      "events on its stream",
+            "achieved": gram_bytes / (roof_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+            "frac": gram_bytes / (roof_ms * 1e-3) / 1e9 / hbm_peak, "traffic": traffic.get("k_oz_rows_dram_bytes"),
+            "peak_source": peak_src, "ms_per_launch": roof_ms, "algorithmic_bytes_per_launch": gram_bytes,
+            "moved_bytes_per_launch": n * d * 13 + 8 * n,
+            "frac_of_moved_bytes": (n * d * 13 + 8 * n) / (roof_ms * 1e-3) / 1e9 / hbm_peak,
+            "dominant_of_step": dominant,
+            "note": "algorithmic bytes = n*(8d+8) (X and y once); the kernel also writes the digit planes (5 B per element), "
+                    "so it moves 13/8 of that: frac_of_moved_bytes is its HBM efficiency"}
+        int8_ops = 11 * 2.0 * 256 * 256 * n
+        tensor = {
+            "bound": "tensor", "kernel": "k_oz_gemm (pass B: 11 exact int8 plane products, tcgen05.mma kind::i8 cta_group::2, "
+                                         "TMA tensor copies, TMEM accumulators) + k_oz_reduce + k_oz_finish, timed alone "
+                                         "(NB_GLM_INT8_PRODUCTS_ONLY)",
+            "ms_per_launch": parts["products_ms"], "achieved": int8_ops / (parts["products_ms"] * 1e-3) / 1e12,
+            "peak": INT8_TOPS_NOMINAL, "unit": "TOP/s", "frac": int8_ops / (parts["products_ms"] * 1e-3) / 1e12 / INT8_TOPS_NOMINAL,
+            "peak_source": "nominal dense int8 (4.5 POP/s); MEASURED_PEAKS.json has no int8 figure",
+            "traffic": traffic.get("k_oz_gemm_dram_bytes"),
+            "equivalent_fp64_tflops": useful_flops / (parts["products_ms"] * 1e-3) / 1e12}
+    else:
+        roofline = {
+            "bound": "fp64", "kernel": "k_tri_gram (warp-specialised upper-triangular X^T diag(w) X, FP64 DMMA fed by TMA bulk "
+                                       "copies) + k_fused_finish, timed alone with CUDA events on its stream",
+            "achieved": useful_flops / (tri_ms * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": (useful_flops / (tri_ms * 1e-3) / 1e12 / fp64_peak) if fp64_peak else None,
+            "peak_source": "builder-measured DMMA peak (profiles/fp64_peak.json, tools/fp64_peak.cu)",
+            "traffic": traffic.get("k_tri_gram_dram_bytes"), "ms_per_launch": tri_ms,
+            "hbm_frac": gram_bytes / (tri_ms * 1e-3) / 1e9 / hbm_peak}
+        tensor = None
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -381,42 +637,49 @@ def run_ours(args, result):
         "config": {"workload": "LogisticRegression newton, tall-skinny %dx%d float64 per GPU (BASELINE configs[3]; "
                                "10^8x256 = 8 such shards)" % (n, d),
                    "rows_per_gpu": n, "d": d, "penalty": "l2", "C": 10, "l2_flush": L2_NOTE,
+                   "hessian": "int8 tensor path (exact digit split of x*sqrt(w), csrc/glm_ozaki.cu)" if int8_used
+                              else "fp64 DMMA (csrc/glm_fused.cu)",
                    "step": "one Newton iteration: fused stats pass + all-reduce(p*p+p+1 f64) + Newton update + 8-byte read-back"},
         "fit_sec_per_iteration": ms_step * 1e-3,
         "fit_sec": fit_sec, "fit_iterations": fit_iters,
-        "roofline": {"bound": "hbm",
-                     "kernel": "k_tri_gram (pass 2: warp-specialised upper-triangular X^T diag(w) X, FP64 DMMA fed by TMA "
-                               "bulk copies) + k_fused_finish, timed alone with CUDA events on its stream",
-                     "achieved": gram_bytes / (tri_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": gram_bytes / (tri_ms * 1e-3) / 1e9 / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                     "ms_per_launch": tri_ms, "algorithmic_bytes_per_launch": gram_bytes,
-                     "note": "FP64-tensor-bound at d=256 (32 flop/B vs a balance of ~5.7): the DMMA ceiling is "
-                             "n*d*(d+1)/37.2e12 s = 18% of the HBM peak; see fp64 (tensor roofline) and pass1 (HBM-bound pass)"},
-        "fp64": {"kernel": "k_tri_gram", "ms_per_launch": tri_ms,
-                 "achieved_tflops_sym": gram_flops_sym / (tri_ms * 1e-3) / 1e12,
+        "step_frac_of_hbm": value / world / hbm_peak,
+        "roofline": roofline,
+        "fp64": {"kernel": "k_tri_gram (the FP64 DMMA Hessian, used for heavy-tailed blocks and d outside 129..256)",
+                 "ms_per_launch": tri_ms, "achieved_tflops_useful": useful_flops / (tri_ms * 1e-3) / 1e12,
                  "achieved_tflops_executed": executed_flops / (tri_ms * 1e-3) / 1e12,
-                 "peak_tflops": fp64_peak,
-                 "frac_executed": (executed_flops / (tri_ms * 1e-3) / 1e12 / fp64_peak) if fp64_peak else None},
-        "stats_pass": {"what": "nb_glm_stats(NB_GLM_HESS_NO_OBJECTIVE), what a Newton step runs = pass 1 + pass 2 + finish kernels", "ms_per_launch": gram_ms,
-                       "achieved": gram_bytes / (gram_ms * 1e-3) / 1e9, "unit": "GB/s"},
-        "pass1": {"kernel": "k_glm_rows (eta/link/objective/gradient, HBM-bound)", "ms_per_launch": rows_ms,
-                  "achieved": gram_bytes / (rows_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                  "frac": gram_bytes / (rows_ms * 1e-3) / 1e9 / hbm_peak},
+                 "peak_tflops": fp64_peak, "peak_source": "builder-measured (profiles/fp64_peak.json)",
+                 "frac_useful": (useful_flops / (tri_ms * 1e-3) / 1e12 / fp64_peak) if fp64_peak else None,
+                 "frac_executed": (executed_flops / (tri_ms * 1e-3) / 1e12 / fp64_peak) if fp64_peak else None,
+                 "stats_pass_ms": parts["stats_fp64_ms"]},
+        "stats_pass": {"what": "nb_glm_stats_prepared(NB_GLM_HESS_NO_OBJECTIVE%s): everything a Newton step runs before the update"
+                               % (" | NB_GLM_INT8_HESSIAN" if int8_used else ""),
+                       "ms_per_launch": parts.get("stats_int8_ms", parts["stats_fp64_ms"]),
+                       "achieved": gram_bytes / (parts.get("stats_int8_ms", parts["stats_fp64_ms"]) * 1e-3) / 1e9, "unit": "GB/s"},
+        "gradient_pass": {"kernel": "k_glm_rows (eta/link/objective/gradient: the L-BFGS evaluation, HBM-bound)",
+                          "ms_per_launch": grad_ms, "achieved": gram_bytes / (grad_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                          "unit": "GB/s", "frac": gram_bytes / (grad_ms * 1e-3) / 1e9 / hbm_peak},
+        "prepare_ms": prep_ms,
         "clocks": clocks,
-        # per Newton step: k_glm_rows, k_glm_rows_finish, k_tri_gram, k_fused_finish, k_newton_prep, k_chol_solve, and the
-        # gated fallback pair k_inv / k_newton_apply (launched, exit at once when the Cholesky step succeeded)
-        "gpu_launches": 8 * K,
+        # per Newton step (int8 Hessian): memset, k_oz_rows, TMA-fed k_oz_gemm, k_oz_reduce, k_oz_finish, k_glm_rows_finish,
+        # k_newton_prep, k_chol_solve and the gated fallback pair k_inv / k_newton_apply (exit at once after a good solve);
+        # fp64 Hessian: k_glm_rows, k_glm_rows_finish, k_tri_gram, k_fused_finish + the same four
+        "gpu_launches": (9 if int8_used else 8) * K,
         "coef_checksum": float(np.sum(np.abs(km.get(beta.blocks[(0,)].oid)))),
     }
+    if tensor is not None:
+        line["tensor"] = tensor
+    if pm is not None:
+        line["parity_multi"] = pm
+    if strong is not None:
+        line["strong"] = strong
     if e2e is not None:
         line["e2e"] = e2e
+    if extras is not None:
+        line["extras"] = extras
     if world == 1 and not args.no_cpu_baseline:
-        gbs, dt, cores = cpu_newton_steps(args.cpu_rows, d, args.cpu_steps)
-        line["cpu_baseline"] = {
-            "value": gbs, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d x %d rows (4 row blocks), %d Newton iterations of the reference algorithm "
-                      "(oracle/glm.py), NumPy/OpenBLAS on %d threads, %.2f s/iteration"
-                      % (args.cpu_rows, d, args.cpu_steps, cores, dt)}
+        gbs, dt, cores, kind = cpu_newton_steps(args.cpu_rows, d, args.cpu_steps)
+        line["cpu_baseline"] = {"value": gbs, "unit": UNIT, "cores": cores, "kind": kind,
+                                "sample": cpu_sample_text(args.cpu_rows, d, args.cpu_steps, cores, kind, dt)}
     result["line"] = line
     if world > 1:
         dist.destroy_process_group()

@@ -317,6 +317,10 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
  * 2^-38 * 2^range_log2 (less by ~sqrt(n) for rounding errors of random sign); a caller that needs 1e-10 should
  * take the FP64 path when range_log2 > 5 (heavy-tailed columns, single outliers). */
 #define NB_GLM_INT8_HESSIAN 4
+/* measurement only, together with NB_GLM_INT8_HESSIAN: run just the row pass (link, g, u, digit planes) or just the
+ * integer products + finish on the planes the previous call left in scratch_d */
+#define NB_GLM_INT8_ROWS_ONLY 8
+#define NB_GLM_INT8_PRODUCTS_ONLY 16
 size_t nb_glm_prep_bytes(int64_t d);
 int nb_glm_prepare(int device, const double* x_d, int64_t n, int64_t d, int64_t ldx, void* prep_d,
                    size_t prep_bytes, void* stream);

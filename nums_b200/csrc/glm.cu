@@ -394,7 +394,7 @@ bool oz_applicable(int family, int64_t n, int64_t d, int64_t ldx, const double* 
 size_t oz_scratch_bytes(int device, int64_t n);
 int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                  const double* beta, int skip_obj, const void* prep, double* stats, double* parts, int max_parts,
-                 int* nparts, void* scratch, size_t scratch_bytes, cudaStream_t st);
+                 int* nparts, void* scratch, size_t scratch_bytes, int phases, cudaStream_t st);
 
 struct GlmLayout {
   size_t off_w, off_parts, off_gemm, off_oz, total;
@@ -530,6 +530,7 @@ int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, 
   NB_REQUIRE(ydt == NB_F64 || ydt == NB_I64, "nb_glm_stats: y dtype %d not supported", ydt);
   const int skip_obj = (want_hess & 2) ? 1 : 0;      // NB_GLM_NO_OBJECTIVE
   const bool int8_hess = (want_hess & NB_GLM_INT8_HESSIAN) != 0;
+  const int oz_phases = (want_hess & NB_GLM_INT8_ROWS_ONLY) ? 1 : ((want_hess & NB_GLM_INT8_PRODUCTS_ONLY) ? 2 : 3);
   want_hess &= 1;
   NB_REQUIRE(!int8_hess || prep_d != nullptr, "nb_glm_stats: NB_GLM_INT8_HESSIAN needs the block's nb_glm_prepare output");
   GlmLayout L = glm_layout(device, n, d, want_hess, int8_hess);
@@ -552,10 +553,12 @@ int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, 
     // the same second stage as k_glm_rows
     int np = 0;
     int rc = oz_glm_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, skip_obj, prep_d, stats_d, parts, L.max_parts,
-                          &np, sc + L.off_oz, L.total - L.off_oz, st);
+                          &np, sc + L.off_oz, L.total - L.off_oz, oz_phases, st);
     if (rc) return rc;
-    k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, np, parts, want_hess, stats_d);
-    NB_LAUNCH_CHECK();
+    if (np > 0) {
+      k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, np, parts, want_hess, stats_d);
+      NB_LAUNCH_CHECK();
+    }
     return 0;
   }
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);

@@ -621,9 +621,11 @@ static OzEncodeFn oz_encode_fn() {
 
 // pass A + pass B + finish.  `stats` receives g, objective, the intercept row/column of H (through
 // k_glm_rows_finish, launched by the caller's usual path) and the d x d corner of H.
+// phases: bit 0 = pass A, bit 1 = pass B + finish (both for a normal call; one at a time lets a benchmark time them apart,
+// pass B then works on the planes the previous call left in the scratch).
 int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                  const double* beta, int skip_obj, const void* prep, double* stats, double* parts, int max_parts,
-                 int* nparts, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+                 int* nparts, void* scratch, size_t scratch_bytes, int phases, cudaStream_t st) {
   const OzPlan p = oz_plan(device, n);
   NB_REQUIRE(scratch != nullptr && scratch_bytes >= p.total, "int8 Hessian: scratch too small (%zu < %zu)",
              scratch_bytes, p.total);
@@ -634,8 +636,9 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
   int32_t* part = (int32_t*)(sc + p.off_part);
   int* flag = (int*)(sc + p.off_flag);
   const int ew = family == NB_GLM_LINEAR ? 0 : -1;       // sqrt(w) <= 1 (linear), <= 1/2 (logistic: w = mu (1 - mu))
+  *nparts = 0;
+  if (phases & 1) {
   NB_CHECK(cudaMemsetAsync(flag, 0, sizeof(int), st));
-
   OzRowsArgs ra;
   ra.x = x; ra.n = n; ra.d = d; ra.ldx = ldx; ra.y = y; ra.ydt = ydt; ra.beta = beta; ra.family = family;
   ra.skip_obj = skip_obj; ra.ew = ew; ra.prep = (const OzPrep*)prep; ra.planes = planes;
@@ -652,6 +655,8 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
   k_oz_rows<<<(unsigned)grid, OZ_ROWS_THREADS, 0, st>>>(ra);
   NB_LAUNCH_CHECK();
   *nparts = (int)grid;
+  }
+  if (!(phases & 2)) return 0;
 
   CUtensorMap tm;
   cuuint64_t dims[3] = {(cuuint64_t)OZ_COLS, (cuuint64_t)n, (cuuint64_t)OZ_S};

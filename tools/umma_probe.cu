@@ -171,11 +171,76 @@ __global__ void __launch_bounds__(192) k_probe(const __grid_constant__ CUtensorM
   }
 }
 
+// Issue rate of tcgen05.mma kind::i8 (M = 256 pair, N = 256, K = 32) from resident shared-memory tiles, for MN-major and
+// K-major operand descriptors (the data is whatever the tiles hold: timing only).
+__global__ void __launch_bounds__(64) k_rate(int iters, int kmajor, long long* cycles) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* tiles = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t done_bar;
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  for (int i = threadIdx.x; i < 8 * 8192 / 4; i += 64) ((uint32_t*)tiles)[i] = 0x01010101u * (uint32_t)(i & 3);
+  if (threadIdx.x == 0) { mbar_init(&done_bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(smem_u32(&tmem_base_s)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  cluster_sync();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+  long long t0 = 0, t1 = 0;
+  if (warp == 0 && rank == 0 && lane == 0) {
+    const uint32_t idesc = kmajor ? ((2u << 4) | (1u << 7) | (1u << 10) | ((256u >> 3) << 17) | ((256u >> 4) << 24)) : idesc_i8(256, 256);
+    t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+      const uint32_t a_base = smem_u32(tiles) + (uint32_t)(it & 3) * 8192u, b_base = smem_u32(tiles) + (uint32_t)(4 + (it & 3)) * 8192u;
+      for (int ks = 0; ks < 2; ++ks) {
+        // K-major SW128: rows of 128 bytes (128 k), 8-row groups 1024 bytes apart; K advances 32 bytes inside the row
+        const uint64_t ad = kmajor ? umma_desc(a_base + ks * 32, 16, 1024) : umma_desc(a_base + ks * 32 * HALF, 8192, 8 * HALF);
+        const uint64_t bd = kmajor ? umma_desc(b_base + ks * 32, 16, 1024) : umma_desc(b_base + ks * 32 * HALF, 8192, 8 * HALF);
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}"
+                     :: "r"(tmem_base + (uint32_t)(it & 1) * 256u), "l"(ad), "l"(bd), "r"(idesc), "r"(1u), "r"(0u) : "memory");
+      }
+    }
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(smem_u32(&done_bar)), "h"((uint16_t)3) : "memory");
+  }
+  mbar_wait_bounded(&done_bar, 0);
+  if (warp == 0 && rank == 0 && lane == 0) { t1 = clock64(); cycles[0] = t1 - t0; }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  cluster_sync();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" :: "r"(tmem_base));
+}
+
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static int rate_test() {
+  long long* dc; CK(cudaMalloc(&dc, 8));
+  const size_t smem = 8 * 8192 + 1024;
+  CK(cudaFuncSetAttribute(k_rate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  for (int kmajor = 0; kmajor < 2; ++kmajor)
+    for (int pairs = 1; pairs <= 72; pairs *= 72) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(64); cfg.dynamicSmemBytes = smem;
+      cudaLaunchAttribute at[1]; at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      const int iters = 20000;
+      CK(cudaLaunchKernelEx(&cfg, k_rate, iters, kmajor, dc));
+      CK(cudaDeviceSynchronize());
+      long long c = 0; CK(cudaMemcpy(&c, dc, 8, cudaMemcpyDeviceToHost));
+      printf("rate %s pairs=%d: %.1f clk per MMA (M256 N256 K32)\n", kmajor ? "K-major" : "MN-major", pairs, (double)c / (2.0 * iters));
+    }
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc > 1 && atoi(argv[1]) == 0) return rate_test();
   const int rows = argc > 1 ? atoi(argv[1]) : 256;
   const int pair = argc > 2 ? atoi(argv[2]) : 0;
   std::vector<int8_t> h((size_t)2 * rows * COLS);
