@@ -497,7 +497,8 @@ def run_ours(args, result):
             X = y = None
             torch.cuda.empty_cache()
             free, _ = torch.cuda.mem_get_info()
-            need = rows_s * d * 8 * (1.0 + 5.0 / 8.0) + (6 << 30)
+            # X + one bounded buffer of digit planes (<= 12.52e6 rows) + 2 MiB of int32 partials per 32768 rows + slack
+            need = rows_s * d * 8 + min(rows_s, 12_517_376) * 256 * 5 + (rows_s // 32768 + 1) * (2 << 20) + (8 << 30)
             mode_s = "int8" if free > need else "fp64"
             os.environ["NUMS_B200_HESSIAN"] = mode_s
             X, y, _, _ = tiled_shard(dv, K_, rank, rows_s, d, local)

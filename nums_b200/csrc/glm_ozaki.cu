@@ -40,7 +40,7 @@ constexpr int OZ_S = 5;                 // digit planes
 constexpr int OZ_COLS = 256;            // plane width (columns of X, zero padded)
 constexpr int OZ_HALF = 128;
 constexpr int OZ_KC = 64;               // rows per pipeline stage
-constexpr int OZ_TILES = 20;              // 8 KB tiles of shared memory: a group with np planes runs OZ_TILES / np stages
+constexpr int OZ_TILES = 26;              // 8 KB tiles of shared memory: a group with np planes runs OZ_TILES / np stages
 constexpr int OZ_MAX_STAGES = 8;
 constexpr int OZ_MAX_RANGE = 32768;     // rows per accumulation (int32 headroom)
 constexpr int OZ_GROUPS = 4;
@@ -161,15 +161,47 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
   return r;
 }
 
+constexpr int OZ_ROWS_STAGES = 3;        // batches of OZ_R rows in flight per warp (bulk copies into its own ring)
+
+__device__ __forceinline__ void oz_rows_fetch(const OzRowsArgs& a, int64_t batch, double* stage, uint64_t* bar) {
+  // one lane: rows [batch*R, +R) of X -> stage[R][d] (compact rows), completion on `bar`
+  const int64_t row0 = batch * OZ_R;
+  const int64_t left = a.n - row0;
+  const int rows = left < OZ_R ? (int)left : OZ_R;
+  const unsigned row_bytes = (unsigned)(a.d * sizeof(double));
+  const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bar);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_s), "r"(row_bytes * (unsigned)rows) : "memory");
+  if (a.ldx == a.d) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"((unsigned)__cvta_generic_to_shared(stage)), "l"(a.x + row0 * a.ldx), "r"(row_bytes * (unsigned)rows), "r"(bar_s)
+                 : "memory");
+  } else {
+    for (int r = 0; r < rows; r++)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"((unsigned)__cvta_generic_to_shared(stage + (size_t)r * a.d)), "l"(a.x + (row0 + r) * a.ldx), "r"(row_bytes),
+                      "r"(bar_s) : "memory");
+  }
+}
+
+// Latency, not bandwidth, held the first version (direct 32-byte loads, 8 warps of 228 registers per SM, each warp
+// alternating between waiting for its rows and a ~600-instruction batch) to 4.6 TB/s of combined traffic.  Each warp now
+// keeps OZ_ROWS_STAGES batches in flight as bulk copies into its own shared-memory ring (lane 0 issues the copy for batch
+// i + STAGES - 1 before the warp starts on batch i); no producer warp and no "empty" barriers are needed because the
+// warp that refills a stage is the one that has just finished reading it.
 __global__ void __launch_bounds__(OZ_ROWS_THREADS, 1)
 k_oz_rows(const OzRowsArgs a) {
   constexpr int NW = OZ_ROWS_THREADS / 32;
   constexpr int R = OZ_R;
+  constexpr int NS = OZ_ROWS_STAGES;
+  extern __shared__ __align__(128) double oz_ring[];          // [NW][NS][R][d]
+  __shared__ __align__(8) uint64_t ring_full[NW][NS];
   __shared__ double s_g[OZ_COLS], s_u[OZ_COLS], s_sc[4];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t d = a.d, n = a.n;
   for (int j = tid; j < OZ_COLS; j += OZ_ROWS_THREADS) { s_g[j] = 0.0; s_u[j] = 0.0; }
   if (tid < 4) s_sc[tid] = 0.0;
+  if (tid < NW * NS) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((unsigned)__cvta_generic_to_shared(&ring_full[tid / NS][tid % NS])));
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
 
   // this lane owns columns cA..cA+3 and cB..cB+3 (element slots 0..3 and 4..7)
@@ -198,18 +230,61 @@ k_oz_rows(const OzRowsArgs a) {
 
   const int64_t nbatches = (n + R - 1) / R;
   const int64_t per_it = (int64_t)gridDim.x * NW;
-  for (int64_t batch = (int64_t)blockIdx.x * NW + warp; batch < nbatches; batch += per_it) {
+  const int64_t first = (int64_t)blockIdx.x * NW + warp;
+  double* my_ring = oz_ring + (size_t)warp * NS * R * d;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < NS - 1; s++)
+      if (first + s * per_it < nbatches) oz_rows_fetch(a, first + s * per_it, my_ring + (size_t)s * R * d, &ring_full[warp][s]);
+  }
+  int stage = 0;
+  unsigned phase = 0;
+  // this lane's byte position in every plane for the first row of the batch: advanced once per batch, so that the forty
+  // plane stores of a batch need no address arithmetic beyond constant offsets
+  int8_t* pl[OZ_S];
+#pragma unroll
+  for (int p = 0; p < OZ_S; p++) pl[p] = a.planes + p * a.plane_stride + first * R * OZ_COLS + cA;
+  const int64_t pl_step = per_it * R * OZ_COLS;
+  for (int64_t batch = first; batch < nbatches; batch += per_it) {
     const int64_t row0 = batch * R;
+    // y of the row this lane evaluates: asked for before the wait on the ring, so its latency hides behind it
+    const int64_t myrow = row0 + (lane % R);
+    const bool inb = myrow < n;
+    const double yv = inb ? load_y(a.y, a.ydt, myrow) : 0.0;
+    // refill the stage this warp finished reading in the previous iteration
+    if (lane == 0) {
+      const int64_t ahead = batch + (NS - 1) * per_it;
+      const int sa = stage == 0 ? NS - 1 : stage - 1;
+      if (ahead < nbatches) oz_rows_fetch(a, ahead, my_ring + (size_t)sa * R * d, &ring_full[warp][sa]);
+    }
+    {
+      const unsigned bar_s = (unsigned)__cvta_generic_to_shared(&ring_full[warp][stage]);
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "WAIT_%=:\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+          "@p bra DONE_%=;\n\t"
+          "bra WAIT_%=;\n\t"
+          "DONE_%=:\n\t}"
+          :: "r"(bar_s), "r"(phase) : "memory");
+    }
+    const double* st_rows = my_ring + (size_t)stage * R * d;
     double xv[R][8];
 #pragma unroll
     for (int r = 0; r < R; r++) {
       const int64_t row = row0 + r;
-      const double* xr = a.x + row * a.ldx;
-      if (row < n && vA) ld256(xr + cA, xv[r][0], xv[r][1], xv[r][2], xv[r][3]);
-      else { xv[r][0] = xv[r][1] = xv[r][2] = xv[r][3] = 0.0; }
-      if (row < n && vB) ld256(xr + cB, xv[r][4], xv[r][5], xv[r][6], xv[r][7]);
-      else { xv[r][4] = xv[r][5] = xv[r][6] = xv[r][7] = 0.0; }
+      const double* xr = st_rows + (size_t)r * d;
+      if (row < n && vA) {
+        const double2 p0 = *reinterpret_cast<const double2*>(xr + cA), p1 = *reinterpret_cast<const double2*>(xr + cA + 2);
+        xv[r][0] = p0.x; xv[r][1] = p0.y; xv[r][2] = p1.x; xv[r][3] = p1.y;
+      } else { xv[r][0] = xv[r][1] = xv[r][2] = xv[r][3] = 0.0; }
+      if (row < n && vB) {
+        const double2 p0 = *reinterpret_cast<const double2*>(xr + cB), p1 = *reinterpret_cast<const double2*>(xr + cB + 2);
+        xv[r][4] = p0.x; xv[r][5] = p0.y; xv[r][6] = p1.x; xv[r][7] = p1.y;
+      } else { xv[r][4] = xv[r][5] = xv[r][6] = xv[r][7] = 0.0; }
     }
+    __syncwarp();                                  // every lane holds its part of the stage in registers: it may be refilled
+    if (++stage == NS) { stage = 0; phase ^= 1u; }
     double part[R];
 #pragma unroll
     for (int r = 0; r < R; r++) {
@@ -225,9 +300,6 @@ k_oz_rows(const OzRowsArgs a) {
 #pragma unroll
     for (int r = 1; r < R; r++) if ((lane % R) == r) eta = part[r];
     eta += beta0;
-    const int64_t myrow = row0 + (lane % R);
-    const bool inb = myrow < n;
-    const double yv = inb ? load_y(a.y, a.ydt, myrow) : 0.0;
     LinkOut lo = a.skip_obj ? glm_link_noobj_rt(a.family, eta, yv) : glm_link_rt(a.family, eta, yv);
     if (!inb) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
     const double sw = sqrt(lo.wgt);
@@ -259,22 +331,20 @@ k_oz_rows(const OzRowsArgs a) {
           const uint32_t w0 = prmt(t01a, t23a, 0x5410), w1 = prmt(t01a, t23a, 0x7632);
           const uint32_t w2 = prmt(t01b, t23b, 0x5410), w3 = prmt(t01b, t23b, 0x7632);
           const uint32_t w4 = prmt(prmt(H[0], H[1], 0x0040), prmt(H[2], H[3], 0x0040), 0x5410);
-          int8_t* base = a.planes + row * OZ_COLS + (h ? cB : cA);
-          if (h ? vB : vA) {
-            // plane p holds digit s = 4 - p; signed digit = byte ^ 0x80
-            *reinterpret_cast<uint32_t*>(base + 0 * a.plane_stride) = w4 ^ 0x80808080u;
-            *reinterpret_cast<uint32_t*>(base + 1 * a.plane_stride) = w3 ^ 0x80808080u;
-            *reinterpret_cast<uint32_t*>(base + 2 * a.plane_stride) = w2 ^ 0x80808080u;
-            *reinterpret_cast<uint32_t*>(base + 3 * a.plane_stride) = w1 ^ 0x80808080u;
-            *reinterpret_cast<uint32_t*>(base + 4 * a.plane_stride) = w0 ^ 0x80808080u;
-          } else {
-            // columns beyond d: the planes are read 256 wide, keep them zero
-#pragma unroll
-            for (int p = 0; p < OZ_S; p++) *reinterpret_cast<uint32_t*>(base + p * a.plane_stride) = 0u;
-          }
+          const int off = r * OZ_COLS + h * OZ_HALF;
+          // plane p holds digit s = 4 - p; signed digit = byte ^ 0x80; columns beyond d stay zero (the planes are
+          // read 256 wide)
+          const bool valid = h ? vB : vA;
+          *reinterpret_cast<uint32_t*>(pl[0] + off) = valid ? (w4 ^ 0x80808080u) : 0u;
+          *reinterpret_cast<uint32_t*>(pl[1] + off) = valid ? (w3 ^ 0x80808080u) : 0u;
+          *reinterpret_cast<uint32_t*>(pl[2] + off) = valid ? (w2 ^ 0x80808080u) : 0u;
+          *reinterpret_cast<uint32_t*>(pl[3] + off) = valid ? (w1 ^ 0x80808080u) : 0u;
+          *reinterpret_cast<uint32_t*>(pl[4] + off) = valid ? (w0 ^ 0x80808080u) : 0u;
         }
       }
     }
+#pragma unroll
+    for (int p = 0; p < OZ_S; p++) pl[p] += pl_step;
   }
   if (bad) atomicExch(a.flag, 1);
 
@@ -565,9 +635,16 @@ k_oz_finish(const OzFinishArgs a) {
 // ------------------------------------------------------------------------------------------------ host side
 static inline size_t oz_align(size_t v) { return (v + 1023) & ~(size_t)1023; }
 
+// The digit planes are 5/8 of the size of X: rows are therefore processed in up to OZ_MAX_CHUNKS chunks through one
+// plane buffer of at most ~16 GB (pass A of a chunk, then pass B of the same chunk), so the scratch of the call does
+// not grow with the block beyond that.
+constexpr int OZ_MAX_CHUNKS = 4;                       // the row pass writes per-CTA partials per chunk (max_parts = 4 per SM)
+constexpr int64_t OZ_CHUNK_ROWS = 12517376;            // 382 ranges of 32768 rows (>= the 1.25e7-row benchmark shard)
+
 struct OzPlan {
-  int range_rows, nranges, lanes, pairs;
-  int64_t n_alloc;
+  int range_rows, lanes, pairs;
+  int nchunks; int64_t chunk_rows;      // rows per chunk (the last one may be shorter); a multiple of range_rows
+  int nranges;                          // over all chunks
   size_t off_planes, off_part, off_sums, off_flag, total;
 };
 
@@ -577,16 +654,22 @@ static OzPlan oz_plan(int device, int64_t n) {
   p.pairs = ((sms / 2) / OZ_GROUPS) * OZ_GROUPS;
   if (p.pairs < OZ_GROUPS) p.pairs = OZ_GROUPS;
   p.lanes = p.pairs / OZ_GROUPS;
+  if (n < 1) n = 1;
   int64_t per_lane = (n + p.lanes - 1) / p.lanes;
   int64_t rr = ((per_lane + OZ_KC - 1) / OZ_KC) * OZ_KC;
   if (rr < OZ_KC) rr = OZ_KC;
   if (rr > OZ_MAX_RANGE) rr = OZ_MAX_RANGE;
   p.range_rows = (int)rr;
+  int64_t chunk = OZ_CHUNK_ROWS;
+  if (const char* e = getenv("NUMS_B200_OZ_CHUNK_ROWS")) { const long long v = atoll(e); if (v >= OZ_KC) chunk = v; }   // tests
+  if ((n + chunk - 1) / chunk > OZ_MAX_CHUNKS) chunk = (n + OZ_MAX_CHUNKS - 1) / OZ_MAX_CHUNKS;
+  chunk = ((chunk + rr - 1) / rr) * rr;
+  if (chunk > n) chunk = ((n + rr - 1) / rr) * rr;
+  p.chunk_rows = chunk;
+  p.nchunks = (int)((n + chunk - 1) / chunk);
   p.nranges = (int)((n + rr - 1) / rr);
-  if (p.nranges < 1) p.nranges = 1;
-  p.n_alloc = n > 0 ? n : 1;
   size_t cur = 0;
-  p.off_planes = cur; cur += oz_align((size_t)OZ_S * p.n_alloc * OZ_COLS);
+  p.off_planes = cur; cur += oz_align((size_t)OZ_S * (size_t)p.chunk_rows * OZ_COLS);
   p.off_part = cur; cur += oz_align((size_t)p.nranges * OZ_GROUPS * OZ_SLOTS * 65536 * sizeof(int32_t));
   p.off_sums = cur; cur += oz_align((size_t)OZ_GROUPS * OZ_SLOTS * 65536 * sizeof(long long));
   p.off_flag = cur; cur += 1024;
@@ -637,57 +720,68 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
   int* flag = (int*)(sc + p.off_flag);
   const int ew = family == NB_GLM_LINEAR ? 0 : -1;       // sqrt(w) <= 1 (linear), <= 1/2 (logistic: w = mu (1 - mu))
   *nparts = 0;
-  if (phases & 1) {
-  NB_CHECK(cudaMemsetAsync(flag, 0, sizeof(int), st));
-  OzRowsArgs ra;
-  ra.x = x; ra.n = n; ra.d = d; ra.ldx = ldx; ra.y = y; ra.ydt = ydt; ra.beta = beta; ra.family = family;
-  ra.skip_obj = skip_obj; ra.ew = ew; ra.prep = (const OzPrep*)prep; ra.planes = planes;
-  ra.plane_stride = p.n_alloc * OZ_COLS; ra.partials = parts; ra.flag = flag;
-  int64_t want = ((n + OZ_R - 1) / OZ_R + (OZ_ROWS_THREADS / 32) - 1) / (OZ_ROWS_THREADS / 32);
-  int64_t grid = (int64_t)dev_info(device).sms * 2;
+  if (phases & 1) NB_CHECK(cudaMemsetAsync(flag, 0, sizeof(int), st));
   static KernelSetup rows_setup;
   int occ = 1;
-  if (int rc = rows_setup.get(device, k_oz_rows, OZ_ROWS_THREADS, 0, &occ)) return rc;
-  grid = (int64_t)dev_info(device).sms * occ;
-  if (grid > max_parts) grid = max_parts;
-  if (grid > want) grid = want;
-  if (grid < 1) grid = 1;
-  k_oz_rows<<<(unsigned)grid, OZ_ROWS_THREADS, 0, st>>>(ra);
-  NB_LAUNCH_CHECK();
-  *nparts = (int)grid;
-  }
-  if (!(phases & 2)) return 0;
-
-  CUtensorMap tm;
-  cuuint64_t dims[3] = {(cuuint64_t)OZ_COLS, (cuuint64_t)n, (cuuint64_t)OZ_S};
-  cuuint64_t strides[2] = {(cuuint64_t)OZ_COLS, (cuuint64_t)p.n_alloc * OZ_COLS};
-  cuuint32_t box[3] = {OZ_HALF, OZ_KC, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult cr = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  NB_REQUIRE(cr == CUDA_SUCCESS, "int8 Hessian: cuTensorMapEncodeTiled failed (%d)", (int)cr);
-
-  OzGemmArgs ga;
-  ga.n = n; ga.range_rows = p.range_rows; ga.nranges = p.nranges; ga.lanes = p.lanes; ga.part = part;
+  const size_t rows_smem = (size_t)(OZ_ROWS_THREADS / 32) * OZ_ROWS_STAGES * OZ_R * OZ_COLS * sizeof(double);
+  if (int rc = rows_setup.get(device, k_oz_rows, OZ_ROWS_THREADS, rows_smem, &occ)) return rc;
   const size_t smem = (size_t)OZ_TILES * OZ_TILE + 1024;
   static bool gemm_ready[NB_MAX_DEVICES] = {};
   if (device < 0 || device >= NB_MAX_DEVICES || !gemm_ready[device]) {
     NB_CHECK(cudaFuncSetAttribute(k_oz_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (device >= 0 && device < NB_MAX_DEVICES) gemm_ready[device] = true;
   }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(2 * p.pairs));
-  cfg.blockDim = dim3(192);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  cfg.attrs = at; cfg.numAttrs = 1;
-  NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm, tm, ga));
+  const int item = 8;                    // y is float64 or int64
+  int ranges_done = 0;
+  for (int c = 0; c < p.nchunks; c++) {
+    const int64_t c0 = (int64_t)c * p.chunk_rows;
+    const int64_t cn = (n - c0 < p.chunk_rows) ? n - c0 : p.chunk_rows;
+    const int cranges = (int)((cn + p.range_rows - 1) / p.range_rows);
+    if (phases & 1) {
+      OzRowsArgs ra;
+      ra.x = x + c0 * ldx; ra.n = cn; ra.d = d; ra.ldx = ldx; ra.y = (const char*)y + c0 * item; ra.ydt = ydt; ra.beta = beta;
+      ra.family = family; ra.skip_obj = skip_obj; ra.ew = ew; ra.prep = (const OzPrep*)prep; ra.planes = planes;
+      ra.plane_stride = p.chunk_rows * OZ_COLS; ra.flag = flag;
+      int64_t want = ((cn + OZ_R - 1) / OZ_R + (OZ_ROWS_THREADS / 32) - 1) / (OZ_ROWS_THREADS / 32);
+      int64_t grid = (int64_t)dev_info(device).sms * occ;
+      if (grid > max_parts / p.nchunks) grid = max_parts / p.nchunks;
+      if (grid > want) grid = want;
+      if (grid < 1) grid = 1;
+      ra.partials = parts + (size_t)(*nparts) * (2 * d + 3);
+      k_oz_rows<<<(unsigned)grid, OZ_ROWS_THREADS, rows_smem, st>>>(ra);
+      NB_LAUNCH_CHECK();
+      *nparts += (int)grid;
+    }
+    if (phases & 2) {
+      CUtensorMap tm;
+      cuuint64_t dims[3] = {(cuuint64_t)OZ_COLS, (cuuint64_t)cn, (cuuint64_t)OZ_S};
+      cuuint64_t strides[2] = {(cuuint64_t)OZ_COLS, (cuuint64_t)p.chunk_rows * OZ_COLS};
+      cuuint32_t box[3] = {OZ_HALF, OZ_KC, 1};
+      cuuint32_t estr[3] = {1, 1, 1};
+      CUresult cr = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      NB_REQUIRE(cr == CUDA_SUCCESS, "int8 Hessian: cuTensorMapEncodeTiled failed (%d)", (int)cr);
+      OzGemmArgs ga;
+      ga.n = cn; ga.range_rows = p.range_rows; ga.nranges = cranges; ga.lanes = p.lanes;
+      ga.part = part + (size_t)ranges_done * OZ_GROUPS * OZ_SLOTS * 65536;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)(2 * p.pairs));
+      cfg.blockDim = dim3(192);
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = st;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm, tm, ga));
+    }
+    ranges_done += cranges;
+  }
+  if (!(phases & 2)) return 0;
 
   long long* sums = (long long*)(sc + p.off_sums);
-  k_oz_reduce<<<dev_info(device).sms * 4, 256, 0, st>>>(part, p.nranges, sums);
+  k_oz_reduce<<<dev_info(device).sms * 4, 256, 0, st>>>(part, ranges_done, sums);
   NB_LAUNCH_CHECK();
   OzFinishArgs fa;
   fa.d = d; fa.ldc = d + 1; fa.sums = sums; fa.prep = (const OzPrep*)prep; fa.ew = ew;

@@ -222,6 +222,15 @@ def test_hessian_int8_tensor_path_and_fp64_path(app, hessian, family, n, d, ldx,
         assert np.all(H[3, :-1] == 0.0) and np.all(H[:-1, 3] == 0.0)
 
 
+def test_hessian_int8_row_chunks(app, monkeypatch):
+    """Rows go through one bounded buffer of digit planes in up to four chunks (12.5e6 rows each at full size); with the
+    chunk size turned down the same code path runs on a small block: 4 chunks, the last one ragged."""
+    monkeypatch.setenv("NUMS_B200_OZ_CHUNK_ROWS", "65536")
+    (H, g, obj), (H0, g0, obj0) = raw_stats(230_001, 256, "logistic", np.int64, seed=21, hessian="int8!")
+    assert rel_err(g, g0) < STAT_TOL and rel_err(obj, obj0) < STAT_TOL and rel_err(H, H0) < STAT_TOL
+    assert np.array_equal(H, H.T)
+
+
 def test_hessian_int8_rejects_a_foreign_column_scale(app):
     """The digit split relies on the block's own column maxima.  Handing the kernel the scales of another block
     (values up to 1000x larger than prepared for) must not give a plausible Hessian: H comes back NaN."""
