@@ -339,6 +339,29 @@ int nb_glm_newton_update(int device, int64_t p, double* stats_d, const double* l
                          const double* beta_d, double* beta_out_d, double* gmax_d,
                          int32_t* info_d, void* scratch_d, size_t scratch_bytes, void* stream);
 
+/* L-BFGS (nums/models/lbfgs.py) on a device-resident workspace: the memory of m (s, y) pairs is a ring in HBM, and
+ * the p-sized algebra the reference runs as dozens of block-array calls per iteration is three launches.
+ *   nb_lbfgs_direction  dir = -H g by the two-loop recursion (LBFGS.get_p :86-100 with H = gamma I, get_H :78-84),
+ *                       slope_d[0] = g . dir
+ *   nb_lbfgs_trial      out = theta + alpha dir                                     (the line-search trial point :47,:51)
+ *   nb_lbfgs_judge      BackTrackingLineSearch's test (:45-48): rejected iff f_t is NaN or f_t > f + c alpha slope.
+ *                       verdict_d[0] = 1 / 0.  On acceptance (or `force`, the min_alpha exit :50) with `remember`, the
+ *                       pair (theta_t - theta, g_t - g) enters the ring with rho = 1 / (s.y + 1e-30) and
+ *                       gamma = s.y / (y.y + 1e-30) (LBFGSMemory :55-62) and verdict_d[1] = max |g_t| (converged() :157).
+ * The workspace (nb_lbfgs_ws_bytes) is owned by the caller; nb_lbfgs_reset empties the ring.  All vectors are
+ * contiguous float64 of length p on `device`; f / slope / verdict are device scalars, so one 16-byte read-back per
+ * trial is the only host synchronisation. */
+size_t nb_lbfgs_ws_bytes(int64_t p, int m);
+int nb_lbfgs_reset(int device, int64_t p, int m, void* ws_d, size_t ws_bytes, void* stream);
+int nb_lbfgs_direction(int device, int64_t p, int m, void* ws_d, const double* g_d, double* dir_d,
+                       double* slope_d, void* stream);
+int nb_lbfgs_trial(int device, int64_t p, const double* theta_d, const double* dir_d, double alpha,
+                   double* out_d, void* stream);
+int nb_lbfgs_judge(int device, int64_t p, int m, void* ws_d, const double* theta_d, const double* g_d,
+                   const double* f_d, const double* theta_t_d, const double* g_t_d, const double* f_t_d,
+                   const double* slope_d, double alpha, double c, int force, int remember,
+                   double* verdict_d, void* stream);
+
 /* mu = link_inv(X.beta[:d] + beta[d]) for predict / forward (glms.py:194-197). */
 int nb_glm_predict(int device, int family, const double* x_d, int64_t n, int64_t d, int64_t ldx,
                    const double* beta_d, double* mu_d, void* stream);

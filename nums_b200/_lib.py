@@ -74,6 +74,12 @@ SIGNATURES = {
                                       c_vp, c_sz, c_vp]),
     "nb_glm_newton_scratch_bytes": (c_sz, [c_i64]),
     "nb_glm_newton_update": (c_int, [c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "nb_lbfgs_ws_bytes": (c_sz, [c_i64, c_int]),
+    "nb_lbfgs_reset": (c_int, [c_int, c_i64, c_int, c_vp, c_sz, c_vp]),
+    "nb_lbfgs_direction": (c_int, [c_int, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "nb_lbfgs_trial": (c_int, [c_int, c_i64, c_vp, c_vp, c_dbl, c_vp, c_vp]),
+    "nb_lbfgs_judge": (c_int, [c_int, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_dbl, c_dbl, c_int,
+                               c_int, c_vp, c_vp]),
     "nb_glm_predict": (c_int, [c_int, c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp]),
 }
 

@@ -272,6 +272,73 @@ k_newton_apply(int64_t p, const double* __restrict__ hinv, const double* __restr
   }
 }
 
+// The whole Newton update for p <= 32 in one warp (the README fit has p = 3): penalty, max|g|, the solve of
+// H delta = g by Gaussian elimination with partial pivoting in shared memory, beta_out = beta - delta.  At this size the
+// three-kernel path (prep, cooperative Cholesky with grid barriers, gated inverse + apply) is four launches and ~60 us
+// of latency for a few hundred flops.  info = k + 1 when column k has no non-zero pivot (np.linalg.inv raises then).
+__global__ void __launch_bounds__(32)
+k_newton_small(int p, double* __restrict__ stats, const double* __restrict__ l2vec, const double* __restrict__ beta,
+               double* __restrict__ beta_out, double* __restrict__ gmax, int32_t* __restrict__ info) {
+  __shared__ double A[32][33];
+  __shared__ double rhs[32];
+  const int lane = threadIdx.x;
+  const double* H = stats;
+  const double* g = stats + (size_t)p * p;
+  double gv = 0.0;
+  if (lane < p) {
+    const double l = l2vec ? l2vec[lane] : 0.0;
+    gv = g[lane] + (l2vec ? l * beta[lane] : 0.0);
+    for (int c = 0; c < p; c++) A[lane][c] = H[(size_t)lane * p + c] + (c == lane ? l : 0.0);
+    rhs[lane] = gv;
+  }
+  // max |g| with NumPy's rule: a NaN propagates
+  double m = lane < p ? fabs(gv) : 0.0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ov = __shfl_xor_sync(0xffffffffu, m, o);
+    m = (isnan(m) || isnan(ov)) ? nan("") : (ov > m ? ov : m);
+  }
+  __syncwarp();
+  int bad = 0;
+  for (int k = 0; k < p; k++) {
+    // pivot: largest |A[r][k]|, r >= k (first such row on ties, like getrf)
+    double best = (lane >= k && lane < p) ? fabs(A[lane][k]) : -1.0;
+    int who = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int ow = __shfl_xor_sync(0xffffffffu, who, o);
+      if (ob > best || (ob == best && ow < who)) { best = ob; who = ow; }
+    }
+    if (!(best > 0.0)) { bad = k + 1; break; }
+    if (who != k) {               // swap rows k and who (lane = column)
+      if (lane < p) { const double t = A[k][lane]; A[k][lane] = A[who][lane]; A[who][lane] = t; }
+      if (lane == 0) { const double t = rhs[k]; rhs[k] = rhs[who]; rhs[who] = t; }
+    }
+    __syncwarp();
+    const double piv = A[k][k];
+    if (lane > k && lane < p) {
+      const double f = A[lane][k] / piv;
+      for (int c = k + 1; c < p; c++) A[lane][c] = fma(-f, A[k][c], A[lane][c]);
+      rhs[lane] = fma(-f, rhs[k], rhs[lane]);
+    }
+    __syncwarp();
+  }
+  if (!bad) {
+    // back substitution: lane 0 walks the rows (p <= 32)
+    if (lane == 0) {
+      for (int r = p - 1; r >= 0; r--) {
+        double s = rhs[r];
+        for (int c = r + 1; c < p; c++) s = fma(-A[r][c], rhs[c], s);
+        rhs[r] = s / A[r][r];
+      }
+    }
+    __syncwarp();
+    if (lane < p) beta_out[lane] = beta[lane] - rhs[lane];
+  }
+  if (lane == 0) { *gmax = m; *info = bad; }
+}
+
 // newton_chol.cu
 int newton_chol_solve(int device, int64_t p, const double* h, double* l, const double* g, const double* beta,
                       double* beta_out, double* z, int* flag, int32_t* info, cudaStream_t st);
@@ -307,6 +374,11 @@ int nb_glm_newton_update(int device, int64_t p, double* stats_d, const double* l
   int* flag = (int*)sp; sp += 256;
   void* inv_sc = sp;
   const size_t inv_bytes = scratch_bytes - (size_t)(sp - (char*)scratch_d);
+  if (p <= 32 && !NB_ENV_FLAG("NUMS_B200_NEWTON_INVERSE")) {
+    k_newton_small<<<1, 32, 0, st>>>((int)p, stats_d, l2vec_d, beta_d, beta_out_d, gmax_d, info_d);
+    NB_LAUNCH_CHECK();
+    return 0;
+  }
   k_newton_prep<<<1, 256, 0, st>>>(p, stats_d, l2vec_d, beta_d, gmax_d);
   NB_LAUNCH_CHECK();
   const int* gate = nullptr;

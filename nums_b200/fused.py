@@ -117,6 +117,30 @@ def glm_newton_update(stats, l2vec, beta):
     return out, gmax, info
 
 
+def glm_newton_step(stats, l2vec, beta):
+    """glm_newton_update with its two scalars in ONE 16-byte block (max|g| as float64, then info as int32), so that
+    the convergence test of an iteration is a single read-back: -> (beta_new, verdict)."""
+    lib = _lib.load()
+    dev = stats.device_index
+    beta = dv.contiguous(dv.to_device(beta, dev))
+    p = beta.shape[0]
+    if stats.shape != (p * p + p + 1,):
+        raise ValueError("stats length %s does not match p=%d" % (stats.shape, p))
+    l2 = dv.contiguous(dv.to_device(l2vec, dev)) if l2vec is not None else None
+    out = dv.empty((p,), np.float64, dev)
+    verdict = dv.empty((2,), np.float64, dev)
+    sc = dv.scratch(lib.nb_glm_newton_scratch_bytes(p), dev)
+    _lib.check(lib.nb_glm_newton_update(dev, p, stats.ptr, l2.ptr if l2 is not None else None, beta.ptr, out.ptr,
+                                        verdict.ptr, verdict.ptr + 8, sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+    return out, verdict
+
+
+def read_verdict(values):
+    """(max|g|, info) from the host copy of a glm_newton_step verdict."""
+    values = np.ascontiguousarray(values, dtype=np.float64)
+    return float(values[0]), int(values[1:2].view(np.int32)[0])
+
+
 def glm_predict(x, beta, family):
     lib = _lib.load()
     dev = x.device_index
@@ -157,5 +181,6 @@ def register(km):
     km.register("stats_add_g", stats_add_g, {})
     km.register("glm_stats", glm_stats, {})
     km.register("glm_newton_update", glm_newton_update, {})
+    km.register("glm_newton_step", glm_newton_step, {})
     km.register("glm_predict", glm_predict, {})
     km.register("stats_slice", stats_slice, {})

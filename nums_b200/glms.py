@@ -460,13 +460,19 @@ def newton(model, beta, X, y, tol, max_iter):
                 # contribution is zero (:266-272)
                 extra = model._l1penalty_vec * app.map_uop("sign", beta)
                 stats = km.call("stats_add_g", stats, extra.blocks[(0,)].oid, syskwargs=sk)
-            b_new, gmax, info = km.call("glm_newton_update", stats, l2, beta.blocks[(0,)].oid, syskwargs=sk)
+            b_new, verdict = km.call("glm_newton_step", stats, l2, beta.blocks[(0,)].oid, syskwargs=sk)
             beta = BlockArray.from_oid(b_new, (p,), np.float64, km)
             model.n_iter_ += 1
-            gm, inf = km.get([gmax, info])      # the one host sync per iteration (glms.py:674)
-            if int(np.asarray(inf).reshape(-1)[0]) != 0:
+            gm, inf = _fused.read_verdict(km.get(verdict))      # the one host sync per iteration (glms.py:674)
+            if inf != 0:
+                if gm != gm:
+                    # a NaN/Inf reached g or H (diverged eta, non-finite X): np.linalg.inv returns NaNs without
+                    # raising and the reference's loop runs on with beta = NaN until max_iter (glms.py:673-675);
+                    # the result is the same NaN vector, returned at once
+                    beta = app.array(np.full(p, np.nan), (p,))
+                    break
                 raise np.linalg.LinAlgError("Singular matrix")
-            if float(gm) <= tol:
+            if gm <= tol:
                 break
         return beta
     tol_ba = app.scalar(tol)

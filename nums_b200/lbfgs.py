@@ -1,125 +1,121 @@
-"""L-BFGS with backtracking line search: the algorithm of nums/models/lbfgs.py (two-loop recursion
-:86-100, memory :55-62, line search :37-52, driver :102-155; constants m=10, rho=1e-2, c=1e-4,
-alpha0=1, alpha_min=1e-30, eps=1e-30).
+"""L-BFGS with a backtracking line search for the GLM models: what nums/models/lbfgs.py computes (memory of m = 10
+pairs, rho = 1e-2, c = 1e-4, alpha0 = 1, alpha_min = 1e-30, the 1e-30 guards), organised for the device.
 
-The p-sized vector algebra runs through the block kernels exactly as the reference schedules it
-(including the dense gamma*I "H @ q" product, :78-84,96).  What changes is the cost of an evaluation:
-with a fused model every f(theta) is ONE pass over X that returns the objective AND the gradient, so
-the accepted trial's gradient is reused instead of the reference's two extra passes (:136-138).
+The optimiser state never leaves HBM.  `DeviceLBFGS` owns a workspace (ring of (s, y) pairs, rho, gamma) and drives
+three entry points of libnumsb200 (csrc/lbfgs.cu): the two-loop recursion is ONE launch instead of ~12 block-array
+calls per memory slot, a trial point is one launch, and the Armijo test, the memory update and max|g| are one launch
+whose 16-byte verdict is the only thing the host reads per trial.  Every evaluation of the objective is one fused pass
+over X that also returns the gradient, so the accepted trial's gradient is reused (the reference pays two more passes
+per iteration, lbfgs.py:136-138, and one per line search for f(theta), :44).
 """
 import numpy as np
 
-from .blockarray import BlockArray
+from . import _lib
+from . import device as dv
+from .device import DeviceBlock
+
+MEMORY = 10
+SHRINK = 1e-2
+ARMIJO_C = 1e-4
+ALPHA_MIN = 1e-30
 
 
-class LBFGSMemory:
-    def __init__(self, k, s, y):
-        self.k = k
-        self.s = s
-        self.y = y
-        ys_inner = s.transpose(defer=True) @ y
-        self.rho = 1.0 / (ys_inner + 1e-30)
-        self.gamma = ys_inner / (y.transpose(defer=True) @ y + 1e-30)
+class DeviceLBFGS:
+    """Workspace + the three kernels, for contiguous float64 vectors of length p on one device."""
+
+    def __init__(self, p, device_index, m=MEMORY):
+        self.p, self.m, self.dev = int(p), int(m), device_index
+        self.lib = _lib.load()
+        self.ws = dv.scratch(self.lib.nb_lbfgs_ws_bytes(self.p, self.m), device_index)
+        self.slope = dv.empty((1,), np.float64, device_index)
+        self.verdict = dv.empty((2,), np.float64, device_index)
+        _lib.check(self.lib.nb_lbfgs_reset(device_index, self.p, self.m, self.ws.data_ptr(), self.ws.numel(), self._st()))
+
+    def _st(self):
+        return dv.stream_ptr(self.dev)
+
+    def direction(self, g):
+        d = dv.empty((self.p,), np.float64, self.dev)
+        _lib.check(self.lib.nb_lbfgs_direction(self.dev, self.p, self.m, self.ws.data_ptr(), g.ptr, d.ptr, self.slope.ptr,
+                                               self._st()))
+        return d
+
+    def trial(self, theta, direction, alpha):
+        out = dv.empty((self.p,), np.float64, self.dev)
+        _lib.check(self.lib.nb_lbfgs_trial(self.dev, self.p, theta.ptr, direction.ptr, float(alpha), out.ptr, self._st()))
+        return out
+
+    def judge(self, theta, g, f, theta_t, g_t, f_t, alpha, force, remember):
+        """-> (accepted, max|g_t|): the one host read of a trial."""
+        _lib.check(self.lib.nb_lbfgs_judge(self.dev, self.p, self.m, self.ws.data_ptr(), theta.ptr, g.ptr, f.ptr, theta_t.ptr,
+                                           g_t.ptr, f_t.ptr, self.slope.ptr, float(alpha), ARMIJO_C, int(force), int(remember),
+                                           self.verdict.ptr, self._st()))
+        v = dv.to_numpy(self.verdict)
+        return bool(v[0] != 0.0), float(v[1])
 
 
-class BackTrackingLineSearch:
-    def __init__(self, model):
-        self.app = model._app
-        self.model = model
+def _packed(vec):
+    """A 1-d BlockArray as one contiguous float64 block."""
+    from .glms import _gather_single_block
+    return dv.contiguous(_gather_single_block(vec))
 
-    def f(self, X, y, theta):
-        """-> (objective, gradient or None)"""
-        m = self.model
-        if m._fused:
-            return m.objective_and_gradient(X, y, theta)
-        return m.objective(X, y, theta, m.forward(X, theta)), None
 
-    def execute(self, X, y, theta, grad, p, f_val=None, rho=1.0e-1, init_alpha=1.0, c=1e-4, min_alpha=1e-10):
-        """Returns (alpha, f(theta + alpha p), gradient there or None)."""
-        alpha = init_alpha
-        if f_val is None:
-            f_val, _ = self.f(X, y, theta)
-        f_next, g_next = self.f(X, y, theta + alpha * p)
-        slope = grad.transpose(defer=True) @ p
-        while self.app.isnan(f_next) or f_next > f_val + c * alpha * slope:
-            alpha *= rho
-            if alpha < min_alpha:
-                return min_alpha, None, None
-            f_next, g_next = self.f(X, y, theta + alpha * p)
-        return max(alpha, min_alpha), f_next, g_next
+def _scalar_block(ba):
+    """A 0-d BlockArray as a (1,) device block."""
+    return DeviceBlock(dv.contiguous(ba.blocks[()].oid).t.reshape(1))
 
 
 class LBFGS:
-    def __init__(self, model, m=10, max_iter=100, thresh=1e-4, dtype=np.float64):
-        self.app = model._app
-        self.model = model
-        self.m = m
-        self.max_iter = max_iter
-        self.thresh = thresh
-        self.dtype = dtype
-        self.k = 0
-        self.identity = None
-        self.memory = [None] * m
-        self.ls = BackTrackingLineSearch(model)
+    def __init__(self, model, m=MEMORY, max_iter=100, thresh=1e-4):
+        self.model, self.m, self.max_iter, self.thresh = model, m, max_iter, thresh
 
-    def get_H(self):
-        if self.k == 0:
-            return self.identity
-        mem = self.memory[-1]
-        assert mem.k == self.k - 1
-        return mem.gamma * self.identity
-
-    def get_p(self, H, g):
-        q = g
-        forward_vars = []
-        for i in range(-1, -self.m - 1, -1):
-            mem_i = self.memory[i]
-            if mem_i is None:
-                break
-            alpha = mem_i.rho * mem_i.s.transpose(defer=True) @ q
-            q = q - alpha * mem_i.y
-            forward_vars.insert(0, (alpha, mem_i))
-        r = H @ q
-        for alpha, mem_i in forward_vars:
-            beta = mem_i.rho * mem_i.y.transpose(defer=True) @ r
-            r = r + mem_i.s * (alpha - beta)
-        return r
-
-    def _gradient(self, X, y, theta):
-        m = self.model
-        if m._fused:
-            return m.objective_and_gradient(X, y, theta)
-        return None, m.gradient(X, y, m.forward(X, theta), theta)
-
-    def execute(self, X, y, theta):
-        if self.k != 0:
-            raise Exception("Unexpected state.")
+    def _evaluate(self, X, y, theta_block, like):
+        """(f, g) at the packed point, as device blocks: one fused pass, or the generic block kernels."""
         model = self.model
-        bs = theta.block_shape[0]
-        self.identity = self.app.eye((theta.shape[0], theta.shape[0]), (bs, bs), dtype=self.dtype)
-        f_val, g = self._gradient(X, y, theta)
-        thresh = self.app.scalar(self.thresh)
+        theta = _as_blockarray(theta_block, like)
+        if model._fused:
+            f, g = model.objective_and_gradient(X, y, theta)
+        else:
+            mu = model.forward(X, theta)
+            f, g = model.objective(X, y, theta, mu), model.gradient(X, y, mu, theta)
+        return _scalar_block(f), _packed(g)
+
+    def execute(self, X, y, theta0):
+        model = self.model
+        theta = _packed(theta0)
+        dev = theta.device_index
+        opt = DeviceLBFGS(theta.shape[0], dev, self.m)
+        f, g = self._evaluate(X, y, theta, theta0)
         model.n_iter_ = 0
-        while self.k < self.max_iter:
-            H = self.get_H()
-            p = -self.get_p(H, g)
-            alpha, f_next, g_next = self.ls.execute(X, y, theta, g, p, f_val=f_val, rho=1e-2, init_alpha=1.0,
-                                                     c=1e-4, min_alpha=1e-30)
-            next_theta = theta + alpha * p
+        for k in range(self.max_iter):
+            last = k + 1 >= self.max_iter
+            direction = opt.direction(g)
+            alpha = 1.0
+            while True:
+                trial = opt.trial(theta, direction, alpha)
+                f_t, g_t = self._evaluate(X, y, trial, theta0)
+                accepted, gmax = opt.judge(theta, g, f, trial, g_t, f_t, alpha, force=False, remember=not last)
+                if accepted:
+                    break
+                alpha *= SHRINK
+                if alpha < ALPHA_MIN:
+                    # lbfgs.py:49-50: the search gives up and the step alpha_min is taken as it is
+                    trial = opt.trial(theta, direction, ALPHA_MIN)
+                    f_t, g_t = self._evaluate(X, y, trial, theta0)
+                    _, gmax = opt.judge(theta, g, f, trial, g_t, f_t, ALPHA_MIN, force=True, remember=not last)
+                    break
+            theta, g, f = trial, g_t, f_t
             model.n_iter_ += 1
-            if self.k + 1 >= self.max_iter:
-                theta = next_theta
+            if last or gmax <= self.thresh:
                 break
-            if g_next is None:
-                f_next, g_next = self._gradient(X, y, next_theta)
-            mem = LBFGSMemory(k=self.k, s=next_theta - theta, y=g_next - g)
-            self.memory.append(mem)
-            self.memory.pop(0)
-            self.k += 1
-            theta, g, f_val = next_theta, g_next, f_next
-            if self.app.max(self.app.abs(g)) <= thresh:
-                break
-        self.k = 0
-        self.identity = None
-        self.memory = [None] * self.m
-        return theta
+        return _as_blockarray(theta, theta0)
+
+
+def _as_blockarray(block, like):
+    """The packed vector as a BlockArray with the grid of `like` (views, no copies)."""
+    from .blockarray import BlockArray
+    out = BlockArray(like.grid.copy(), like.km)
+    for entry in like.grid.get_entry_iterator():
+        lo, hi = like.grid.get_slice_tuples(entry)[0]
+        out.blocks[entry].oid = DeviceBlock(block.t[lo:hi])
+    return out

@@ -123,13 +123,17 @@ def fused_newton(app, model, beta, X, y, tol, max_iter):
         if l1 is not None:
             extra = l1 * app.map_uop("sign", beta)          # L1 term of grad_penalty (glms.py:254-264)
             stats = km.call("stats_add_g", stats, packed(extra), syskwargs=home)
-        b, gmax, info = km.call("glm_newton_update", stats, l2, b, syskwargs={**home, "options": {"num_returns": 3}})
+        b, verdict = km.call("glm_newton_step", stats, l2, b, syskwargs={**home, "options": {"num_returns": 2}})
         if l1 is not None:
             beta = _unpack(BlockArray, km, beta, b, d)
-        gm, inf = km.get([gmax, info])                      # the one host sync per iteration
-        if int(np.asarray(inf).reshape(-1)[0]) != 0:
-            raise np.linalg.LinAlgError("Singular matrix")
-        if float(gm) <= tol_value:
+        gm, inf = _fused.read_verdict(km.get(verdict))      # the one host sync per iteration
+        if inf != 0:
+            if gm == gm:
+                raise np.linalg.LinAlgError("Singular matrix")
+            # non-finite g / H: the reference's inverse returns NaNs and its loop runs on to max_iter with beta = NaN
+            b = km.put(np.full(p, np.nan), syskwargs=home)
+            break
+        if gm <= tol_value:
             break
     return _unpack(BlockArray, km, beta, b, d)
 

@@ -93,6 +93,46 @@ def test_readme_logistic(app, fused):
                            solver="newton-cg", penalty="l2", C=10)
     coef_close(m, g["beta"], g["beta0"])
     np.testing.assert_array_equal(m.predict(Xb).get(), g["pred"])
+    assert m.n_iter_ == int(load_golden("glm_cfg4_d256")["readme_20000_iters"])     # the reference's iteration count
+
+
+@pytest.mark.parametrize("hessian", ["int8", "fp64"])
+def test_cfg4_slice_d256_against_the_reference(app, hessian, monkeypatch):
+    """A 2*10^5 x 256 slice of BASELINE config 4 — the benchmarked kernels (row pass + int8 tensor products, or row pass +
+    FP64 DMMA) — against what the REFERENCE ITSELF produced (tests/golden/make_golden_cfg4.py): coefficients <= 1e-8,
+    the same number of Newton iterations, and g / H / objective at beta = 0 to 1e-10.  The inputs are regenerated on the
+    device from the reference's block-RNG stream, bit for bit (the golden keeps their checksum)."""
+    from nums_b200 import device as dv, fused
+    from nums_b200.blockarray import BlockArray
+    from nums_b200.cuda_kernel import KernelCls
+    from nums_b200.glms import LogisticRegression
+    from nums_b200.grid import ArrayGrid
+    monkeypatch.setenv("NUMS_B200_HESSIAN", hessian)
+    g = load_golden("glm_cfg4_d256")
+    n, d = int(g["cfg4_n"]), int(g["cfg4_d"])
+    half = n // 2
+    K = KernelCls()
+    km = app.km
+    X = BlockArray(ArrayGrid((n, d), (half, d), "float64"), km)
+    y = BlockArray(ArrayGrid((n,), (half,), "int64"), km)
+    shift = dv.from_numpy(np.float64(2.0 * np.sqrt(2.0 / d)), 0)
+    for j in range(2):
+        blk = K.random_block((1337, j), "normal", (0.0, 1.0, half * d), (half, d), np.float64, device_index=0)
+        X.blocks[(j, 0)].oid = blk if j == 0 else K.bop("add", blk, shift, False, False, {})
+        y.blocks[(j,)].oid = dv.from_numpy(np.full(half, j, dtype=np.int64), 0)
+    total = sum(float(dv.to_numpy(K.reduce_axis("sum", X.blocks[(j, 0)].oid, None, False, False))) for j in range(2))
+    assert abs(total - float(g["cfg4_x_checksum"])) <= 1e-9 * abs(float(g["cfg4_x_checksum"]))
+    with pytest.warns(UserWarning):
+        m = LogisticRegression(app=app, solver="newton-cg", penalty="l2", C=10)
+        m.fit(X, y)
+    assert m.n_iter_ == int(g["cfg4_iters"])
+    coef_close(m, g["cfg4_beta"], g["cfg4_beta0"])
+    p = d + 1
+    zero = dv.from_numpy(np.zeros(p), 0)
+    s = sum(dv.to_numpy(fused.glm_stats(X.blocks[(j, 0)].oid, y.blocks[(j,)].oid, zero, "logistic", True)) for j in range(2))
+    assert rel_err(s[: p * p].reshape(p, p), g["cfg4_H0"]) < STAT_TOL
+    assert rel_err(s[p * p: p * p + p], g["cfg4_g0"]) < STAT_TOL
+    assert rel_err(s[p * p + p], g["cfg4_obj0"]) < STAT_TOL
 
 
 @pytest.mark.parametrize("fused", [True, False])

@@ -178,3 +178,43 @@ def test_csv_oracle_matches_reference_blocks():
         assert csvio.read_csv(data, float, ",", True, nw).shape == (257, 5)
     assert np.array_equal(csvio.read_csv_block(g["int_bytes"].tobytes(), 0, len(g["int_bytes"]), np.int64), g["int64_all"])
     assert np.array_equal(csvio.read_csv_block(g["dec_bytes"].tobytes(), 0, len(g["dec_bytes"]), int), g["pyint_all"])
+
+
+def cfg4_inputs(g):
+    """The 2*10^5 x 256 slice of BASELINE config 4 as the reference drew it (tests/golden/make_golden_cfg4.py):
+    nps.random.seed(1337), row block j from Generator(PCG64(1337).jumped(j)).normal, second block shifted."""
+    n, d = int(g["cfg4_n"]), int(g["cfg4_d"])
+    half = n // 2
+    X = np.empty((n, d))
+    for j in range(2):
+        rng = np.random.Generator(np.random.PCG64(1337).jumped(j))
+        X[j * half:(j + 1) * half] = rng.normal(0.0, 1.0, half * d).reshape(half, d)
+    X[half:] += 2.0 * np.sqrt(2.0 / d)
+    y = np.concatenate([np.zeros(half, dtype=np.int64), np.ones(half, dtype=np.int64)])
+    return X, y
+
+
+def test_cfg4_slice_d256_fit_iterations_and_first_statistics():
+    """The benchmarked shape (d = 256): coefficients, the NUMBER of Newton iterations and g / H / objective at beta = 0
+    of the reference itself."""
+    g = load_golden("glm_cfg4_d256")
+    X, y = cfg4_inputs(g)
+    assert abs(float(X.sum()) - float(g["cfg4_x_checksum"])) <= 1e-9 * abs(float(g["cfg4_x_checksum"]))
+    rb = int(g["cfg4_row_blocks"][0])
+    beta, it = oglm.fit("logistic", X, y, rb, solver="newton-cg", penalty="l2", lam=1.0 / 10)
+    assert it == int(g["cfg4_iters"])
+    assert np.max(np.abs(beta[:-1] - g["cfg4_beta"])) < 1e-10 and abs(beta[-1] - g["cfg4_beta0"]) < 1e-10
+    m = oglm.BlockedGLM("logistic", oglm.split_rows(X, rb), oglm.split_rows(y, rb))
+    b0 = np.zeros(X.shape[1] + 1)
+    fwd = m.forward(b0)
+    assert rel_err(m.gradient(b0, fwd), g["cfg4_g0"]) < TOL
+    assert rel_err(m.hessian(b0, fwd), g["cfg4_H0"]) < TOL
+    assert rel_err(m.objective(b0, fwd), g["cfg4_obj0"]) < TOL
+
+
+def test_readme_iteration_counts():
+    g = load_golden("glm_cfg4_d256")
+    r = load_golden("glm_readme")
+    _, it = oglm.fit("logistic", r["X"], r["y"], int(r["row_block"]), solver="newton-cg", penalty="l2", lam=1.0 / 10)
+    assert it == int(g["readme_20000_iters"]) == 8
+    assert int(g["readme_1000000_iters"]) == 8      # what SURVEY.md 8(d) probed for the README's own size
