@@ -196,12 +196,15 @@ size_t nb_reduce_scratch_bytes(int64_t outer, int64_t len, int64_t inner);
 int nb_reduce(int device, int red, int64_t outer, int64_t len, int64_t inner,
               const void* a_d, int adt, void* out_d, int odt, int acc_dt,
               void* scratch_d, size_t scratch_bytes, void* stream);
-/* nb_reduce for callers that have no way to allocate device memory (a foreign-runtime host that only
- * holds borrowed input/output buffers, a plug-in inside a fixed-memory service, code inside a stream
- * capture).  No counterpart in the reference: NumPy allocates its own temporaries.  The split scratch
- * lives in a built-in device array of NB_REDUCE_STATIC_BYTES (1 MiB) per GPU; larger reductions are
- * refused (use nb_reduce).  The first call on a device resolves that array's address and should be
- * made outside stream capture; calls share the array, so calls that may overlap on the GPU race. */
+/* nb_reduce for callers that have no way to allocate device memory: a foreign-runtime host (cgo, JNI,
+ * another process's memory pool) that only holds the input and output buffers it was lent, or a plug-in
+ * inside a service whose HBM budget was fixed at start-up.  No counterpart in the reference: NumPy
+ * allocates its own temporaries.  The split scratch lives in a built-in device array of
+ * NB_REDUCE_STATIC_BYTES (1 MiB) that every GPU loading the library holds until exit; reductions whose
+ * split needs more are refused with an error (use nb_reduce).  The first call on a device resolves that
+ * array's address and should come before any stream capture.  All calls share the array: it keeps the
+ * previous call's partials (every partial that is read is overwritten first), and calls that may
+ * overlap on the GPU race. */
 #define NB_REDUCE_STATIC_BYTES (1u << 20)
 int nb_reduce_static(int device, int red, int64_t outer, int64_t len, int64_t inner,
                      const void* a_d, int adt, void* out_d, int odt, int acc_dt, void* stream);

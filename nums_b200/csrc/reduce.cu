@@ -762,9 +762,8 @@ int nb_where_fill(int device, int64_t n, const void* cond_d, int cond_dt, int nd
 // nb_reduce_static: the reduction for callers that cannot allocate device memory
 // ------------------------------------------------------------------------------------------------
 // Some users of this library only ever hold the input and output pointers somebody else gave them:
-// a cgo/JNI/ctypes host that wraps buffers owned by another runtime's memory pool, a plug-in running
-// inside a service whose HBM budget is fixed at start-up, or code sitting between the begin and end
-// of a stream capture, where cudaMalloc is not permitted.  They have nowhere to get the split-reduction
+// a cgo/JNI/ctypes host that wraps buffers owned by another runtime's memory pool, or a plug-in running
+// inside a service whose HBM budget is fixed at start-up.  They have nowhere to get the split-reduction
 // scratch from, so this variant keeps it inside the library: a fixed array in device memory that is part
 // of the loaded module (every GPU that loads libnumsb200.so carries these NB_REDUCE_STATIC_BYTES until
 // the process exits).
@@ -799,7 +798,7 @@ extern "C" {
 
 // Same contract and same kernels as nb_reduce, minus the scratch arguments.
 //  * The first call on each device performs the address look-up described above.  Make that first call
-//    outside of any stream capture (it is an ordinary synchronous runtime query, not stream work).
+//    before any stream capture (it is an ordinary synchronous runtime query, not stream work).
 //  * A reduction whose split needs more than NB_REDUCE_STATIC_BYTES (1 MiB) is refused with an error;
 //    use nb_reduce with caller-provided scratch for those (nb_reduce_scratch_bytes tells the size).
 //  * All calls on a device share the one array and it keeps whatever the previous call left there.

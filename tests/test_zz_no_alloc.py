@@ -1,10 +1,9 @@
 """nb_reduce_static — the reduction entry point for callers that cannot allocate device memory.
 
 Who needs it: hosts that drive libnumsb200.so with buffers they merely borrow (a cgo / JNI / ctypes
-wrapper around another runtime's memory pool), plug-ins inside services whose HBM budget is fixed at
-start-up, and code between the begin and end of a stream capture, where cudaMalloc is not allowed.
-They cannot supply the split-reduction scratch nb_reduce asks for, so nb_reduce_static keeps a 1 MiB
-scratch array inside the library.
+wrapper around another runtime's memory pool) and plug-ins inside services whose HBM budget is fixed at
+start-up.  They cannot supply the split-reduction scratch nb_reduce asks for, so nb_reduce_static keeps a
+1 MiB scratch array inside the library.
 
 The test calls it through the C ABI and compares with nb_reduce (caller-provided scratch) on the same
 input, twice in a row: the second call runs on an array that still holds the first call's partials,
