@@ -528,3 +528,29 @@ def test_lasso_elasticnet_and_proba(app, fused):
     m, Xb, _ = fit_dev(app, LogisticRegression, g["X"], g["y"], rb, fused=fused, solver="newton", penalty="l2", C=2.0,
                        max_iter=6)
     assert rel_err(m.predict_proba(Xb).get(), s["proba"]) < STAT_TOL
+
+
+def test_one_process_two_devices(monkeypatch):
+    """The reference's single-driver model (grid.py:172): one process, G devices, row block i on GPU i, partial statistics
+    moved by peer copies and summed by the FIFO tree.  Needs two GPUs (skipped on a one-GPU box)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from nums_b200.app import make_app
+    from nums_b200.glms import LogisticRegression
+    app2 = make_app(num_gpus=2)
+    rng = np.random.default_rng(31)
+    n, d, rb = 60_000, 256, 30_000
+    X = rng.standard_normal((n, d)) + 0.1
+    y = (X @ np.linspace(-0.2, 0.2, d) + 0.3 * rng.standard_normal(n) > 0).astype(np.int64)
+    want, it = oglm.fit("logistic", X, y, rb, solver="newton", penalty="l2", lam=0.1)
+    for mode in ("int8", "fp64"):
+        monkeypatch.setenv("NUMS_B200_HESSIAN", mode)
+        Xb, yb = app2.array(X, block_shape=(rb, d)), app2.array(y, block_shape=(rb,))
+        assert [Xb.blocks[(i, 0)].oid.device_index for i in range(2)] == [0, 1]
+        m = LogisticRegression(app=app2, solver="newton", penalty="l2", C=10)
+        m.fit(Xb, yb)
+        got = np.concatenate([m._beta.get(), [float(m._beta0.get())]])
+        assert np.max(np.abs(got - want)) < COEF_TOL and m.n_iter_ == it
+    x = app2.array(rng.random(200_000), block_shape=(100_000,))
+    assert rel_err((x.T @ x).get(), float(x.get() @ x.get())) < STAT_TOL
