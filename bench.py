@@ -554,6 +554,17 @@ def run_ours(args, result):
             return m._beta_full.get()
 
         fit_from_host()                      # warm-up (allocator, pinned path)
+        # the upload alone, to attribute the end-to-end time (PCIe Gen5 x16: ~55 GB/s per GPU when the host can feed it)
+        barrier()
+        t0 = time.perf_counter()
+        up = app.array(Xh, block_shape=(e_rows, d))
+        torch.cuda.synchronize()
+        upload_s = time.perf_counter() - t0
+        del up
+        if world > 1:
+            tu = torch.tensor([upload_s], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tu, op=dist.ReduceOp.MAX)
+            upload_s = float(tu.item())
         barrier()
         t0 = time.perf_counter()
         fit_from_host()
@@ -565,7 +576,9 @@ def run_ours(args, result):
             dt = float(t.item())
         e2e = {"value": world * K * algorithmic_bytes(e_rows, d) / dt / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": (e_rows * (8 * d + 8)) // K, "d2h_bytes_per_step": 8 + 4 + (8 * p) // K,
-               "rows_per_gpu": e_rows, "seconds": dt,
+               "rows_per_gpu": e_rows, "seconds": dt, "upload_seconds": upload_s,
+               "h2d_gbs_per_gpu": e_rows * d * 8 / upload_s / 1e9, "h2d_gbs_aggregate": world * e_rows * d * 8 / upload_s / 1e9,
+               "compute_seconds_expected": K * ms_step * 1e-3,
                "what": "LogisticRegression.fit(host X, host y): upload from pinned host memory + %d Newton "
                        "iterations + coefficient read-back, per rank" % K}
         del Xh, yh

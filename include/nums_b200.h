@@ -335,12 +335,28 @@ int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, 
  *     g += l2vec * beta;  H += diag(l2vec)           (grad_penalty/hessian_penalty :254-272)
  *     beta_out = beta - inv(H) @ g                    (explicit inverse, linalg.py:246-261)
  *     gmax_d[0] = max |g|                             (convergence test :674)
- * l2vec_d may be NULL (no penalty).  info_d as in nb_inv_f64.  scratch: nb_inv_scratch_bytes(p)
+ * l2vec_d may be NULL (no penalty).  info_d as in nb_inv_f64.  stats_d is CONSUMED: the penalty is added to its g and
+ * to the diagonal of its H in place.  scratch: nb_inv_scratch_bytes(p)
  * + 2*p*p*sizeof(double). */
 size_t nb_glm_newton_scratch_bytes(int64_t p);
 int nb_glm_newton_update(int device, int64_t p, double* stats_d, const double* l2vec_d,
                          const double* beta_d, double* beta_out_d, double* gmax_d,
                          int32_t* info_d, void* scratch_d, size_t scratch_bytes, void* stream);
+
+/* newton() of glms.py:660-676 as ONE call: per iteration nb_glm_stats_prepared on every row block, the FIFO pairwise sum
+ * of the partial statistics (BlockArray.tree_reduce, blockarray.py:643-689), nb_glm_newton_update, and the read-back of
+ * the 16-byte verdict that the `max|g| <= tol` test needs (the stream is synchronised once per iteration; nothing else
+ * crosses to the host).  All blocks live on `device`; x_blocks / y_blocks / rows / ldx / preps are HOST arrays of device
+ * pointers and sizes (preps may be NULL, or hold NULL for blocks that take the FP64 Hessian).  beta_d (p doubles) is
+ * updated in place.  iters_out = iterations run, gmax_out = max|g| of the last one, info_out != 0 if the last update
+ * hit a singular or non-finite Hessian (beta_d then holds the iterate before it).  Stops after max_iter iterations or when
+ * max|g| <= tol; tol < 0 runs exactly max_iter iterations. */
+size_t nb_glm_newton_fit_scratch_bytes(int device, int nblocks, int64_t max_rows, int64_t d, int want_hess_flags);
+int nb_glm_newton_fit(int device, int family, int nblocks, const double* const* x_blocks, const int64_t* rows,
+                      int64_t d, const int64_t* ldx, const void* const* y_blocks, int ydt,
+                      const void* const* preps, int want_hess_flags, const double* l2vec_d, double* beta_d,
+                      double tol, int max_iter, int32_t* iters_out, double* gmax_out, int32_t* info_out,
+                      void* scratch_d, size_t scratch_bytes, void* stream);
 
 /* L-BFGS (nums/models/lbfgs.py) on a device-resident workspace: the memory of m (s, y) pairs is a ring in HBM, and
  * the p-sized algebra the reference runs as dozens of block-array calls per iteration is three launches.

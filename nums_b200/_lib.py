@@ -74,6 +74,10 @@ SIGNATURES = {
                                       c_vp, c_sz, c_vp]),
     "nb_glm_newton_scratch_bytes": (c_sz, [c_i64]),
     "nb_glm_newton_update": (c_int, [c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "nb_glm_newton_fit_scratch_bytes": (c_sz, [c_int, c_int, c_i64, c_i64, c_int]),
+    "nb_glm_newton_fit": (c_int, [c_int, c_int, c_int, C.POINTER(c_vp), P_I64, c_i64, P_I64, C.POINTER(c_vp), c_int,
+                                  C.POINTER(c_vp), c_int, c_vp, c_vp, c_dbl, c_int, C.POINTER(C.c_int32),
+                                  C.POINTER(c_dbl), C.POINTER(C.c_int32), c_vp, c_sz, c_vp]),
     "nb_lbfgs_ws_bytes": (c_sz, [c_i64, c_int]),
     "nb_lbfgs_reset": (c_int, [c_int, c_i64, c_int, c_vp, c_sz, c_vp]),
     "nb_lbfgs_direction": (c_int, [c_int, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -13,6 +13,7 @@
 #include "gemm.cuh"
 #include "glm_common.cuh"
 #include <stdlib.h>
+#include <string.h>
 
 namespace nb {
 
@@ -87,26 +88,28 @@ k_glm_small(const double* __restrict__ x, int64_t n, int64_t ldx, const void* __
   }
 }
 
-// Second stage for k_glm_small: sums CTA partials in order and unpacks into the stats buffer.
-__global__ void __launch_bounds__(64)
+// Second stage for k_glm_small: sums the CTA partials in a fixed order (one warp per statistic: a single thread walking
+// ~600 partials was 50 us of a 10 us pass) and unpacks into the stats buffer.
+__global__ void __launch_bounds__(256)
 k_glm_small_finish(int P, int nparts, const double* __restrict__ partials, int want_hess, double* __restrict__ stats) {
   const int NH = P * (P + 1) / 2;
   const int NV = NH + P + 1;
-  __shared__ double tot[64];
-  for (int j = threadIdx.x; j < NV; j += 64) {
-    double s = 0.0;
-    for (int c = 0; c < nparts; c++) s += partials[(size_t)c * NV + j];
-    tot[j] = s;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    if (want_hess) {
-      int q = 0;
-      for (int i = 0; i < P; i++)
-        for (int j = i; j < P; j++) { stats[i * P + j] = tot[q]; stats[j * P + i] = tot[q]; q++; }
+  const int lane = threadIdx.x & 31;
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < NV; j += gridDim.x * 8) {
+    const double s = sum_partials_warp(partials + j, (size_t)NV, nparts);
+    if (lane != 0) continue;
+    if (j < NH) {
+      if (want_hess) {
+        int i = 0, rem = j;                       // j -> (i, c) of the row-major upper triangle
+        while (rem >= P - i) { rem -= P - i; i++; }
+        const int c = i + rem;
+        stats[i * P + c] = s; stats[c * P + i] = s;
+      }
+    } else if (j < NH + P) {
+      stats[P * P + (j - NH)] = s;
+    } else {
+      stats[P * P + P] = s;
     }
-    for (int j = 0; j < P; j++) stats[P * P + j] = tot[NH + j];
-    stats[P * P + P] = tot[NH + P];
   }
 }
 
@@ -441,7 +444,8 @@ static int launch_small(int device, const double* x, int64_t n, int64_t ldx, con
   if (blocks < 1) blocks = 1;
   k_glm_small<FAMILY, D><<<(unsigned)blocks, GLM_THREADS, 0, st>>>(x, n, ldx, y, ydt, beta, want_hess, parts);
   NB_LAUNCH_CHECK();
-  k_glm_small_finish<<<1, 64, 0, st>>>(D + 1, (int)blocks, parts, want_hess, stats);
+  constexpr int NVS = (D + 1) * (D + 2) / 2 + D + 2;
+  k_glm_small_finish<<<(NVS + 7) / 8, 256, 0, st>>>(D + 1, (int)blocks, parts, want_hess, stats);
   NB_LAUNCH_CHECK();
   return 0;
 }
@@ -613,6 +617,88 @@ int nb_glm_predict(int device, int family, const double* x_d, int64_t n, int64_t
   int64_t cap = (int64_t)dev_info(device).sms * 8;
   k_glm_predict<<<(unsigned)(blocks < cap ? blocks : cap), GLM_THREADS, 0, st>>>(family, x_d, n, d, ldx, beta_d, mu_d);
   NB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// The whole Newton loop (glms.py:660-676) driven from native code
+// ------------------------------------------------------------------------------------------------
+// newton() is a host loop: statistics per row block, the FIFO sum of the partials (blockarray.py:643-689), the update,
+// and one scalar comparison that needs the device's answer.  Driven from Python every one of those steps costs tens of
+// microseconds of interpreter and allocator time; on the README problem (10^6 x 2: 24 MB, ~5 us per pass) that is all
+// of the run time.  Here the same launches are issued back to back from C++, and the 16-byte verdict of an iteration is the
+// only thing read back (one cudaMemcpyAsync + stream synchronise per iteration, as the reference's `<= tol` test implies).
+namespace nb {
+static inline size_t fit_align(size_t v) { return (v + 255) & ~(size_t)255; }
+}
+
+extern "C" {
+
+size_t nb_glm_newton_fit_scratch_bytes(int device, int nblocks, int64_t max_rows, int64_t d, int want_hess_flags) {
+  const int64_t p = d + 1;
+  const size_t len = (size_t)nb_glm_stats_len(d) * sizeof(double);
+  return nb::fit_align(len) * (size_t)(2 * nblocks) + nb::fit_align((size_t)p * sizeof(double)) + 256 +
+         nb::fit_align(nb_glm_newton_scratch_bytes(p)) + nb::fit_align(nb_glm_scratch_bytes(device, max_rows, d, want_hess_flags));
+}
+
+int nb_glm_newton_fit(int device, int family, int nblocks, const double* const* x_blocks, const int64_t* rows, int64_t d,
+                      const int64_t* ldx, const void* const* y_blocks, int ydt, const void* const* preps,
+                      int want_hess_flags, const double* l2vec_d, double* beta_d, double tol, int max_iter,
+                      int32_t* iters_out, double* gmax_out, int32_t* info_out, void* scratch_d, size_t scratch_bytes,
+                      void* stream) {
+  NB_ENTER(device);
+  NB_REQUIRE(nblocks >= 1 && max_iter >= 0, "nb_glm_newton_fit: bad nblocks=%d max_iter=%d", nblocks, max_iter);
+  int64_t max_rows = 0;
+  for (int b = 0; b < nblocks; b++) if (rows[b] > max_rows) max_rows = rows[b];
+  NB_REQUIRE(scratch_d != nullptr && scratch_bytes >= nb_glm_newton_fit_scratch_bytes(device, nblocks, max_rows, d, want_hess_flags),
+             "nb_glm_newton_fit: scratch too small");
+  const int64_t p = d + 1;
+  const int64_t len = nb_glm_stats_len(d);
+  const size_t slot = nb::fit_align((size_t)len * sizeof(double));
+  char* sp = (char*)scratch_d;
+  char* stats0 = sp; sp += slot * (size_t)(2 * nblocks);
+  double* beta_new = (double*)sp; sp += nb::fit_align((size_t)p * sizeof(double));
+  double* verdict = (double*)sp; sp += 256;                  // [max|g| (f64) | info (i32)]
+  void* nsc = sp; const size_t nsc_bytes = nb::fit_align(nb_glm_newton_scratch_bytes(p)); sp += nsc_bytes;
+  void* gsc = sp; const size_t gsc_bytes = scratch_bytes - (size_t)(sp - (char*)scratch_d);
+  auto buf = [&](int i) { return (double*)(stats0 + slot * (size_t)i); };
+  *iters_out = 0; *gmax_out = 0.0; *info_out = 0;
+  // the verdict lands in page-locked host memory (one small buffer per calling thread, allocated on first use): a copy
+  // into pageable memory goes through the driver's staging buffer and costs ~10 us more per iteration
+  static thread_local double* host_verdict = nullptr;
+  if (host_verdict == nullptr) NB_CHECK(cudaHostAlloc((void**)&host_verdict, 64, cudaHostAllocDefault));
+  double* cur = beta_d;                          // iterates ping-pong between beta_d and beta_new
+  double* nxt = beta_new;
+  for (int it = 0; it < max_iter; it++) {
+    for (int b = 0; b < nblocks; b++) {
+      const void* prep = preps ? preps[b] : nullptr;
+      const int mode = prep ? want_hess_flags : (want_hess_flags & ~NB_GLM_INT8_HESSIAN);
+      int rc = nb_glm_stats_prepared(device, family, x_blocks[b], rows[b], d, ldx[b], y_blocks[b], ydt, cur, mode, prep,
+                                     buf(b), gsc, gsc_bytes, stream);
+      if (rc) return rc;
+    }
+    // the reference's FIFO tree: pop two, push their sum at the back
+    int head = 0, tail = nblocks;                // live partials are buffers head .. tail-1 of a queue that only grows
+    while (tail - head > 1) {
+      int rc = nb_bop_reduce(device, NB_RSUM, len, buf(head), buf(head + 1), buf(tail), NB_F64, stream);
+      if (rc) return rc;
+      head += 2; tail += 1;
+    }
+    int rc = nb_glm_newton_update(device, p, buf(head), l2vec_d, cur, nxt, verdict, (int32_t*)(verdict + 1), nsc,
+                                  nsc_bytes, stream);
+    if (rc) return rc;
+    NB_CHECK(cudaMemcpyAsync(host_verdict, verdict, 16, cudaMemcpyDeviceToHost, st));
+    NB_CHECK(cudaStreamSynchronize(st));
+    int32_t info = 0;
+    memcpy(&info, &host_verdict[1], sizeof(int32_t));
+    *iters_out = it + 1; *gmax_out = host_verdict[0]; *info_out = info;
+    if (info != 0) break;                        // singular / non-finite: `cur` is the last good iterate, the caller decides
+    double* t = cur; cur = nxt; nxt = t;
+    if (host_verdict[0] <= tol) break;           // glms.py:674 (the gradient from before the update)
+  }
+  if (cur != beta_d) NB_CHECK(cudaMemcpyAsync(beta_d, cur, (size_t)p * sizeof(double), cudaMemcpyDeviceToDevice, st));
   return 0;
 }
 

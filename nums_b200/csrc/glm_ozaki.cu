@@ -59,10 +59,14 @@ __constant__ OzProduct c_oz_products[OZ_GROUPS][3] = {
     {{0, 0, 3}, {0, 1, 2}, {1, 0, 0}},       // level 3 | level 0
     {{0, 0, 4}, {0, 1, 3}, {1, 0, 1}},       // level 4, pairs p < p' | level 1
     {{0, 1, 4}, {0, 2, 3}, {1, 2, 2}},       // level 5 | level 4, (2,2)
-    {{0, 0, 2}, {1, 1, 1}, {-1, 0, 0}},      // level 2: (0,2) | (1,1)
+    {{0, 0, 2}, {1, 1, 1}, {0, 3, -1}},      // level 2: (0,2) | (1,1); and plane 3 times a tile of zeros (see below)
 };
-__constant__ int c_oz_nplanes[OZ_GROUPS] = {4, 4, 4, 3};
-__constant__ int c_oz_planes[OZ_GROUPS][4] = {{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 3, 4}, {0, 1, 2, 0}};
+// Every group stages four planes and issues three products per stage, so the four pairs of a lane advance at the same pace
+// and stay close: the pair that asks for a tile first pays the trip to HBM, the others find it in L2 (and, being served
+// faster, catch up rather than fall behind).  Group 3 has only two useful products on three planes; its third is plane 3
+// against a tile of zeros (adds nothing to the accumulator) -- the idle tensor time buys the lock step.
+__constant__ int c_oz_nplanes[OZ_GROUPS] = {4, 4, 4, 4};
+__constant__ int c_oz_planes[OZ_GROUPS][4] = {{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 3, 4}, {0, 1, 2, 3}};
 // slot (group, s) -> level and kind (1 = pairs p < p': enters as P + P^T; 0 = p == p')
 constexpr int OZ_LEVELS = 6;
 __constant__ int c_oz_slot_level[OZ_GROUPS][OZ_SLOTS] = {{3, 0}, {4, 1}, {5, 4}, {2, 2}};
@@ -79,33 +83,58 @@ constexpr int OZ_PREP_CTAS = 592;
 // ------------------------------------------------------------------------------------------------ prepare
 // Column maxima of |X| (-> the fixed-point scale of each column) and column sums of squares (-> how far the typical
 // entry sits below that scale; fixed summation order, so the verdict does not change from run to run).
+__device__ __forceinline__ void oz_ld256(const double* p, double& a, double& b, double& c, double& d) {
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+
+// 64 threads cover a row with one 32-byte load each (columns 4t .. 4t+3); the four row groups of a CTA take rows
+// 4 apart, four loads in flight per thread.  VEC = false: 8-byte loads for blocks that are not 32-byte aligned.
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 k_oz_colmax(const double* __restrict__ x, int64_t n, int64_t d, int64_t ldx, unsigned long long* __restrict__ maxbits,
             double* __restrict__ sumsq) {
-  const int c = threadIdx.x;
-  unsigned long long m = 0;
-  double q0 = 0.0, q1 = 0.0, q2 = 0.0, q3 = 0.0;
-  if (c < d) {
-    const int64_t stride = gridDim.x;
-    int64_t r = blockIdx.x;
-    for (; r + 3 * stride < n; r += 4 * stride) {
-      const double v0 = x[r * ldx + c], v1 = x[(r + stride) * ldx + c], v2 = x[(r + 2 * stride) * ldx + c],
-                   v3 = x[(r + 3 * stride) * ldx + c];
-      const unsigned long long a0 = (unsigned long long)__double_as_longlong(fabs(v0));
-      const unsigned long long a1 = (unsigned long long)__double_as_longlong(fabs(v1));
-      const unsigned long long a2 = (unsigned long long)__double_as_longlong(fabs(v2));
-      const unsigned long long a3 = (unsigned long long)__double_as_longlong(fabs(v3));
-      m = max(max(m, a0), max(a1, max(a2, a3)));
-      q0 = fma(v0, v0, q0); q1 = fma(v1, v1, q1); q2 = fma(v2, v2, q2); q3 = fma(v3, v3, q3);
+  __shared__ unsigned long long s_m[4][OZ_COLS];
+  __shared__ double s_q[4][OZ_COLS];
+  const int t = threadIdx.x & 63, rg = threadIdx.x >> 6;
+  const int c0 = 4 * t;
+  unsigned long long m[4] = {0, 0, 0, 0};
+  double q[4] = {0.0, 0.0, 0.0, 0.0};
+  const int64_t stride = (int64_t)gridDim.x * 4;
+  auto take = [&](double v, int e) {
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(fabs(v));
+    m[e] = bits > m[e] ? bits : m[e];
+    q[e] = fma(v, v, q[e]);
+  };
+  if (c0 < d) {
+    int64_t r = (int64_t)blockIdx.x * 4 + rg;
+    if constexpr (VEC) {
+      for (; r + 3 * stride < n; r += 4 * stride) {
+        double v[4][4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) oz_ld256(x + (r + k * stride) * ldx + c0, v[k][0], v[k][1], v[k][2], v[k][3]);
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+#pragma unroll
+          for (int e = 0; e < 4; e++) take(v[k][e], e);
+      }
+      for (; r < n; r += stride) {
+        double v0, v1, v2, v3;
+        oz_ld256(x + r * ldx + c0, v0, v1, v2, v3);
+        take(v0, 0); take(v1, 1); take(v2, 2); take(v3, 3);
+      }
+    } else {
+      for (; r < n; r += stride)
+#pragma unroll
+        for (int e = 0; e < 4; e++) if (c0 + e < d) take(x[r * ldx + c0 + e], e);
     }
-    for (; r < n; r += stride) {
-      const double v = x[r * ldx + c];
-      m = max(m, (unsigned long long)__double_as_longlong(fabs(v)));
-      q0 = fma(v, v, q0);
-    }
-    atomicMax(&maxbits[c], m);      // non-negative doubles order like their bit patterns (NaN patterns sort above Inf)
   }
-  sumsq[(size_t)blockIdx.x * OZ_COLS + c] = (q0 + q1) + (q2 + q3);
+#pragma unroll
+  for (int e = 0; e < 4; e++) { s_m[rg][c0 + e] = m[e]; s_q[rg][c0 + e] = q[e]; }
+  __syncthreads();
+  const int c = threadIdx.x;
+  unsigned long long mm = max(max(s_m[0][c], s_m[1][c]), max(s_m[2][c], s_m[3][c]));
+  if (c < d && mm) atomicMax(&maxbits[c], mm);      // non-negative doubles order like their bit patterns (NaN above Inf)
+  sumsq[(size_t)blockIdx.x * OZ_COLS + c] = (s_q[0][c] + s_q[1][c]) + (s_q[2][c] + s_q[3][c]);
 }
 
 __global__ void k_oz_colexp(const unsigned long long* __restrict__ maxbits, const double* __restrict__ sumsq, int nparts,
@@ -152,9 +181,6 @@ struct OzRowsArgs {
   int* flag;                    // set when a value leaves the 39-bit range
 };
 
-__device__ __forceinline__ void ld256(const double* p, double& a, double& b, double& c, double& d) {
-  asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
-}
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
   uint32_t r;
   asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
@@ -430,6 +456,7 @@ __global__ void __launch_bounds__(192, 1)
 k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
   extern __shared__ __align__(1024) uint8_t oz_raw[];
   uint8_t* tiles = (uint8_t*)(((uintptr_t)oz_raw + 1023) & ~(uintptr_t)1023);       // [stage][plane slot][64][128]
+  uint8_t* zero_tile = tiles + (size_t)(OZ_TILES - 1) * OZ_TILE;                      // the last tile stays zero
   __shared__ __align__(8) uint64_t full[OZ_MAX_STAGES], empty[OZ_MAX_STAGES], acc_full, acc_empty;
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -437,8 +464,10 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
   const int pair = blockIdx.x >> 1;
   const int group = pair % OZ_GROUPS, lane_id = pair / OZ_GROUPS;
   const int np = c_oz_nplanes[group];
-  const int nst = OZ_TILES / np;                     // pipeline stages of this group (5 or 6)
+  const int nst = (OZ_TILES - 1) / np;               // pipeline stages of this group
 
+  for (int i = threadIdx.x; i < (int)(OZ_TILE / 16); i += blockDim.x) reinterpret_cast<uint4*>(zero_tile)[i] = make_uint4(0, 0, 0, 0);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // the tensor core reads it through the async proxy
   if (threadIdx.x == 0) {
     for (int s = 0; s < OZ_MAX_STAGES; s++) { oz_mbar_init(&full[s], 2); oz_mbar_init(&empty[s], 1); }
 
@@ -510,7 +539,7 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
             const OzProduct pr = c_oz_products[group][k];
             if (pr.slot < 0) continue;
             const uint32_t abase = stage_base + (uint32_t)pos[pr.pa] * OZ_TILE;
-            const uint32_t bbase = stage_base + (uint32_t)pos[pr.pb] * OZ_TILE;
+            const uint32_t bbase = pr.pb < 0 ? oz_smem(zero_tile) : stage_base + (uint32_t)pos[pr.pb] * OZ_TILE;
             const uint32_t dcol = tmem_base + (uint32_t)pr.slot * 256u;
 #pragma unroll
             for (int ks = 0; ks < OZ_KC / 32; ks++) {
@@ -813,9 +842,11 @@ int nb_glm_prepare(int device, const double* x_d, int64_t n, int64_t d, int64_t 
   double* sumsq = (double*)(maxbits + OZ_COLS);
   NB_CHECK(cudaMemsetAsync(maxbits, 0, OZ_COLS * sizeof(unsigned long long), st));
   int64_t grid = OZ_PREP_CTAS;
-  if (grid > n) grid = n;
+  if (grid > (n + 3) / 4) grid = (n + 3) / 4;
   if (n > 0) {
-    k_oz_colmax<<<(unsigned)grid, 256, 0, st>>>(x_d, n, d, ldx, maxbits, sumsq);
+    const bool vec = (d % 4 == 0) && (ldx % 4 == 0) && ((((uintptr_t)x_d) & 31) == 0);
+    if (vec) k_oz_colmax<true><<<(unsigned)grid, 256, 0, st>>>(x_d, n, d, ldx, maxbits, sumsq);
+    else k_oz_colmax<false><<<(unsigned)grid, 256, 0, st>>>(x_d, n, d, ldx, maxbits, sumsq);
     NB_LAUNCH_CHECK();
   }
   k_oz_colexp<<<1, 256, 0, st>>>(maxbits, sumsq, n > 0 ? (int)grid : 0, n, d, (OzPrep*)prep_d);

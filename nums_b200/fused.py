@@ -135,6 +135,48 @@ def glm_newton_step(stats, l2vec, beta):
     return out, verdict
 
 
+def glm_newton_fit(family, beta, l2vec, tol, max_iter, hessian, *blocks):
+    """The whole Newton loop in one library call (nb_glm_newton_fit).  blocks = X row blocks followed by the matching y
+    blocks, all on one device.  -> (beta_new, [iterations, max|g|, info])."""
+    lib = _lib.load()
+    nb = len(blocks) // 2
+    xs, ys = list(blocks[:nb]), [dv.contiguous(b) for b in blocks[nb:]]
+    dev = xs[0].device_index
+    d = xs[0].shape[1]
+    p = d + 1
+    for i, x in enumerate(xs):
+        if x.ndim != 2 or x.dtype != np.dtype(np.float64) or x.shape[1] != d or x.device_index != dev:
+            raise TypeError("glm_newton_fit: row blocks must be 2-d float64 of one width on one device")
+        if x.strides[1] != 1:
+            xs[i] = dv.contiguous(x)
+        if ys[i].shape != (xs[i].shape[0],) or ys[i].dtype != ys[0].dtype or ys[i].dtype == np.dtype(np.bool_):
+            raise TypeError("glm_newton_fit: y blocks must match the row blocks (float64 or int64)")
+    out = dv.empty((p,), np.float64, dev)
+    dv.copy_into(out.t, dv.contiguous(dv.to_device(beta, dev)).t)      # blocks are immutable: iterate on a copy
+    l2 = dv.contiguous(dv.to_device(l2vec, dev)) if l2vec is not None else None
+    mode = 3                                                            # NB_GLM_HESS_NO_OBJECTIVE
+    preps = [None] * nb
+    choice = hessian or default_hessian()
+    if choice in ("int8", "int8!"):
+        for i, x in enumerate(xs):
+            if int8_hessian_applies(x, family):
+                found = glm_prepare(x)
+                if found.usable or choice == "int8!":
+                    preps[i] = found.buf.data_ptr()
+        if any(pp is not None for pp in preps):
+            mode |= NB_GLM_INT8_HESSIAN
+    import ctypes as C
+    VP, I64 = C.c_void_p * nb, C.c_int64 * nb
+    rows = [x.shape[0] for x in xs]
+    sc = dv.scratch(lib.nb_glm_newton_fit_scratch_bytes(dev, nb, max(rows), d, mode), dev)
+    iters, gmax, info = C.c_int32(0), C.c_double(0.0), C.c_int32(0)
+    _lib.check(lib.nb_glm_newton_fit(
+        dev, hl.FAMILY_CODE[family], nb, VP(*[x.ptr for x in xs]), I64(*rows), d, I64(*[x.strides[0] for x in xs]),
+        VP(*[y.ptr for y in ys]), ys[0].code, VP(*preps), mode, l2.ptr if l2 is not None else None, out.ptr, float(tol),
+        int(max_iter), C.byref(iters), C.byref(gmax), C.byref(info), sc.data_ptr(), sc.numel(), dv.stream_ptr(dev)))
+    return out, [int(iters.value), float(gmax.value), int(info.value)]
+
+
 def read_verdict(values):
     """(max|g|, info) from the host copy of a glm_newton_step verdict."""
     values = np.ascontiguousarray(values, dtype=np.float64)
@@ -182,5 +224,6 @@ def register(km):
     km.register("glm_stats", glm_stats, {})
     km.register("glm_newton_update", glm_newton_update, {})
     km.register("glm_newton_step", glm_newton_step, {})
+    km.register("glm_newton_fit", glm_newton_fit, {})
     km.register("glm_predict", glm_predict, {})
     km.register("stats_slice", stats_slice, {})

@@ -453,6 +453,22 @@ def newton(model, beta, X, y, tol, max_iter):
             l2 = model._l2penalty_vec.blocks[(0,)].oid
         sk = {"grid_entry": (0,), "grid_shape": (1,)}
         p = beta.shape[0]
+        R = X.grid.grid_shape[0]
+        sharded = model._sharded if model._sharded is not None else (_dist() is not None)
+        one_device = len({X.blocks[(i, 0)].oid.device_index for i in range(R)}) == 1
+        if (not sharded and one_device and (model._l1penalty_vec is None or poisson_skip)
+                and not any(X.blocks[(i, 0)].transposed for i in range(R)) and max_iter > 0):
+            # every row block on one GPU and no collective in the loop: the loop itself runs in the library
+            # (nb_glm_newton_fit); the host sees one call per fit instead of ~5 per iteration
+            oids = [X.blocks[(i, 0)].oid for i in range(R)] + [y.blocks[(i,)].oid for i in range(R)]
+            b_new, (iters, gm, inf) = km.call("glm_newton_fit", model.family, beta.blocks[(0,)].oid, l2, float(tol),
+                                               int(max_iter), None, *oids, syskwargs=X.blocks[(0, 0)].syskwargs())
+            model.n_iter_ = iters
+            if inf != 0:
+                if gm != gm:          # non-finite g / H: the reference's loop ends with beta = NaN (see below)
+                    return app.array(np.full(p, np.nan), (p,))
+                raise np.linalg.LinAlgError("Singular matrix")
+            return BlockArray.from_oid(b_new, (p,), np.float64, km)
         for _ in range(max_iter):
             stats = model.fused_stats(X, y, beta, True, need_obj=False)     # newton() never evaluates the objective
             if model._l1penalty_vec is not None and not poisson_skip:
