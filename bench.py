@@ -440,7 +440,7 @@ def run_ours(args, result):
                                              stats_d.ptr, scratch.data_ptr(), scratch.numel(), st))
 
     if int8_used:
-        INT8, ROWS, PROD = fused.NB_GLM_INT8_HESSIAN, 8, 16
+        INT8, ROWS, PROD = fused.int8_flags(prep, n), 8, 16          # what the step runs (level 5 left out at this n)
         sc8 = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 3 | INT8), local)
         pp = prep.buf.data_ptr()
         parts["stats_int8_ms"] = event_ms(torch, lambda: stats_call(3 | INT8, pp, sc8), reps)
@@ -624,9 +624,10 @@ def run_ours(args, result):
             "dominant_of_step": dominant,
             "note": "algorithmic bytes = n*(8d+8) (X and y once); the kernel also writes the digit planes (5 B per element), "
                     "so it moves 13/8 of that: frac_of_moved_bytes is its HBM efficiency"}
-        int8_ops = 11 * 2.0 * 256 * 256 * n
+        nprod = 9 if (fused.int8_flags(prep, n) & fused.NB_GLM_INT8_NO_LEVEL5) else 11
+        int8_ops = nprod * 2.0 * 256 * 256 * n
         tensor = {
-            "bound": "tensor", "kernel": "k_oz_gemm (pass B: 11 exact int8 plane products, tcgen05.mma kind::i8 cta_group::2, "
+            "bound": "tensor", "kernel": "k_oz_gemm (pass B: %d exact int8 plane products," % nprod + " tcgen05.mma kind::i8 cta_group::2, "
                                          "TMA tensor copies, TMEM accumulators) + k_oz_reduce + k_oz_finish, timed alone "
                                          "(NB_GLM_INT8_PRODUCTS_ONLY)",
             "ms_per_launch": parts["products_ms"], "achieved": int8_ops / (parts["products_ms"] * 1e-3) / 1e12,

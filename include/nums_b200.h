@@ -322,6 +322,10 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
 #define NB_GLM_INT8_HESSIAN 4
 /* measurement only, together with NB_GLM_INT8_HESSIAN: run just the row pass (link, g, u, digit planes) or just the
  * integer products + finish on the planes the previous call left in scratch_d */
+/* with NB_GLM_INT8_HESSIAN: leave out the two least significant of the eleven plane products (the level-5 terms).  Their
+ * relative contribution to H is ~ 2^(2 r - 38.6) / sqrt(n) (r = range_log2 of nb_glm_prepare, n rows): the caller sets this
+ * when that is far below its tolerance (nums_b200.fused: <= 1e-11), which takes a quarter off the operand traffic */
+#define NB_GLM_INT8_NO_LEVEL5 32
 #define NB_GLM_INT8_ROWS_ONLY 8
 #define NB_GLM_INT8_PRODUCTS_ONLY 16
 size_t nb_glm_prep_bytes(int64_t d);

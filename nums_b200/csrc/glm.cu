@@ -397,7 +397,7 @@ bool oz_applicable(int family, int64_t n, int64_t d, int64_t ldx, const double* 
 size_t oz_scratch_bytes(int device, int64_t n);
 int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                  const double* beta, int skip_obj, const void* prep, double* stats, double* parts, int max_parts,
-                 int* nparts, void* scratch, size_t scratch_bytes, int phases, cudaStream_t st);
+                 int* nparts, void* scratch, size_t scratch_bytes, int phases, int scheme, cudaStream_t st);
 
 struct GlmLayout {
   size_t off_w, off_parts, off_gemm, off_oz, total;
@@ -535,6 +535,7 @@ int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, 
   const int skip_obj = (want_hess & 2) ? 1 : 0;      // NB_GLM_NO_OBJECTIVE
   const bool int8_hess = (want_hess & NB_GLM_INT8_HESSIAN) != 0;
   const int oz_phases = (want_hess & NB_GLM_INT8_ROWS_ONLY) ? 1 : ((want_hess & NB_GLM_INT8_PRODUCTS_ONLY) ? 2 : 3);
+  const int oz_scheme = (want_hess & NB_GLM_INT8_NO_LEVEL5) ? 1 : 0;
   want_hess &= 1;
   NB_REQUIRE(!int8_hess || prep_d != nullptr, "nb_glm_stats: NB_GLM_INT8_HESSIAN needs the block's nb_glm_prepare output");
   GlmLayout L = glm_layout(device, n, d, want_hess, int8_hess);
@@ -557,7 +558,7 @@ int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, 
     // the same second stage as k_glm_rows
     int np = 0;
     int rc = oz_glm_stats(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, skip_obj, prep_d, stats_d, parts, L.max_parts,
-                          &np, sc + L.off_oz, L.total - L.off_oz, oz_phases, st);
+                          &np, sc + L.off_oz, L.total - L.off_oz, oz_phases, oz_scheme, st);
     if (rc) return rc;
     if (np > 0) {
       k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, np, parts, want_hess, stats_d);
@@ -674,7 +675,7 @@ int nb_glm_newton_fit(int device, int family, int nblocks, const double* const* 
   for (int it = 0; it < max_iter; it++) {
     for (int b = 0; b < nblocks; b++) {
       const void* prep = preps ? preps[b] : nullptr;
-      const int mode = prep ? want_hess_flags : (want_hess_flags & ~NB_GLM_INT8_HESSIAN);
+      const int mode = prep ? want_hess_flags : (want_hess_flags & ~(NB_GLM_INT8_HESSIAN | NB_GLM_INT8_NO_LEVEL5));
       int rc = nb_glm_stats_prepared(device, family, x_blocks[b], rows[b], d, ldx[b], y_blocks[b], ydt, cur, mode, prep,
                                      buf(b), gsc, gsc_bytes, stream);
       if (rc) return rc;

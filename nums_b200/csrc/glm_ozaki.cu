@@ -41,7 +41,7 @@ constexpr int OZ_COLS = 256;            // plane width (columns of X, zero padde
 constexpr int OZ_HALF = 128;
 constexpr int OZ_KC = 64;               // rows per pipeline stage
 constexpr int OZ_TILES = 26;              // 8 KB tiles of shared memory: a group with np planes runs OZ_TILES / np stages
-constexpr int OZ_MAX_STAGES = 8;
+constexpr int OZ_MAX_STAGES = 12;
 constexpr int OZ_MAX_RANGE = 32768;     // rows per accumulation (int32 headroom)
 constexpr int OZ_GROUPS = 4;
 constexpr int OZ_SLOTS = 2;
@@ -53,24 +53,33 @@ constexpr int OZ_VBITS = 38;            // |v| < 2^38
 // products of each group: {slot, plane of A, plane of B}; planes the group stages.  Levels 0..5 (11 products, 8 slots:
 // the first dropped terms, level 6, are 2^-48 of the column scale squared).
 struct OzProduct { int slot, pa, pb; };
-// Grouping rule: no group stages more than four planes (the TMA tensor copies of a stage, 64 x 128-byte rows per plane and
-// CTA, are the tighter budget: five planes per stage held the whole kernel to the pace of that one group).
-__constant__ OzProduct c_oz_products[OZ_GROUPS][3] = {
-    {{0, 0, 3}, {0, 1, 2}, {1, 0, 0}},       // level 3 | level 0
-    {{0, 0, 4}, {0, 1, 3}, {1, 0, 1}},       // level 4, pairs p < p' | level 1
-    {{0, 1, 4}, {0, 2, 3}, {1, 2, 2}},       // level 5 | level 4, (2,2)
-    {{0, 0, 2}, {1, 1, 1}, {0, 3, -1}},      // level 2: (0,2) | (1,1); and plane 3 times a tile of zeros (see below)
+// Two schemes.  0: levels 0..5, 11 products (any n).  1: levels 0..4, 9 products: the level-5 terms (1,4), (2,3) are sums of
+// n products of independent, zero-mean low digits, i.e. a relative contribution ~ 2^(2r - 38.6) / sqrt(n) to H (r = range_log2
+// of nb_glm_prepare); the caller drops them (NB_GLM_INT8_NO_LEVEL5) when that is below 1e-11 — at 1.25e7 Gaussian rows it is
+// 3e-13 — which removes four of the sixteen plane streams, and this kernel is bound by the L2 -> SM operand stream (measured:
+// time = streamed bytes / 6.6 TB/s in every variant tried).
+// Grouping rule of scheme 0: no group stages more than four planes; every group stages four planes and issues three products per
+// stage, so the four pairs of a lane advance at the same pace and stay close: the pair that asks for a tile first pays the
+// trip to HBM, the others find it in L2.  Group 3 has only two useful products on three planes; its third is plane 3 against a
+// tile of zeros (pb = -1, adds nothing) -- the idle tensor time buys the lock step (DRAM re-reads 2.1x -> 1.66x).
+constexpr int OZ_SCHEMES = 2;
+__constant__ OzProduct c_oz_products[OZ_SCHEMES][OZ_GROUPS][3] = {
+    {{{0, 0, 3}, {0, 1, 2}, {1, 0, 0}},        // level 3 | level 0
+     {{0, 0, 4}, {0, 1, 3}, {1, 0, 1}},        // level 4, pairs p < p' | level 1
+     {{0, 1, 4}, {0, 2, 3}, {1, 2, 2}},        // level 5 | level 4, (2,2)
+     {{0, 0, 2}, {1, 1, 1}, {0, 3, -1}}},      // level 2: (0,2) | (1,1); plane 3 x zeros
+    {{{0, 0, 3}, {0, 1, 2}, {1, 0, 0}},        // level 3 | level 0
+     {{0, 0, 4}, {0, 1, 3}, {1, 0, 1}},        // level 4, pairs p < p' | level 1
+     {{0, 2, 2}, {1, 1, 1}, {-1, 0, 0}},       // level 4, (2,2) | level 2, (1,1)
+     {{0, 0, 2}, {-1, 0, 0}, {-1, 0, 0}}},     // level 2, (0,2) | (slot 1 unused)
 };
-// Every group stages four planes and issues three products per stage, so the four pairs of a lane advance at the same pace
-// and stay close: the pair that asks for a tile first pays the trip to HBM, the others find it in L2 (and, being served
-// faster, catch up rather than fall behind).  Group 3 has only two useful products on three planes; its third is plane 3
-// against a tile of zeros (adds nothing to the accumulator) -- the idle tensor time buys the lock step.
-__constant__ int c_oz_nplanes[OZ_GROUPS] = {4, 4, 4, 4};
-__constant__ int c_oz_planes[OZ_GROUPS][4] = {{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 3, 4}, {0, 1, 2, 3}};
-// slot (group, s) -> level and kind (1 = pairs p < p': enters as P + P^T; 0 = p == p')
+__constant__ int c_oz_nplanes[OZ_SCHEMES][OZ_GROUPS] = {{4, 4, 4, 4}, {4, 4, 2, 2}};
+__constant__ int c_oz_planes[OZ_SCHEMES][OZ_GROUPS][4] = {{{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 3, 4}, {0, 1, 2, 3}},
+                                                          {{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 0, 0}, {0, 2, 0, 0}}};
+// slot (group, s) -> level (-1: unused) and kind (1 = pairs p < p': enters as P + P^T; 0 = p == p')
 constexpr int OZ_LEVELS = 6;
-__constant__ int c_oz_slot_level[OZ_GROUPS][OZ_SLOTS] = {{3, 0}, {4, 1}, {5, 4}, {2, 2}};
-__constant__ int c_oz_slot_off[OZ_GROUPS][OZ_SLOTS] = {{1, 0}, {1, 1}, {1, 0}, {1, 0}};
+__constant__ int c_oz_slot_level[OZ_SCHEMES][OZ_GROUPS][OZ_SLOTS] = {{{3, 0}, {4, 1}, {5, 4}, {2, 2}}, {{3, 0}, {4, 1}, {4, 2}, {2, -1}}};
+__constant__ int c_oz_slot_off[OZ_SCHEMES][OZ_GROUPS][OZ_SLOTS] = {{{1, 0}, {1, 1}, {1, 0}, {1, 0}}, {{1, 0}, {1, 1}, {0, 0}, {1, 0}}};
 
 struct OzPrep {               // nb_glm_prepare output (device memory)
   int32_t colexp[OZ_COLS];    // max|x[:, i]| < 2^colexp[i];  INT32_MIN for an all-zero column
@@ -265,6 +274,8 @@ k_oz_rows(const OzRowsArgs a) {
   }
   int stage = 0;
   unsigned phase = 0;
+  long long ynext = 0;                      // y (float64 or int64: 8 bytes either way) of this lane's row in the next batch
+  if (first < nbatches && first * R + (lane % R) < n) ynext = reinterpret_cast<const long long*>(a.y)[first * R + (lane % R)];
   // this lane's byte position in every plane for the first row of the batch: advanced once per batch, so that the forty
   // plane stores of a batch need no address arithmetic beyond constant offsets
   int8_t* pl[OZ_S];
@@ -273,10 +284,15 @@ k_oz_rows(const OzRowsArgs a) {
   const int64_t pl_step = per_it * R * OZ_COLS;
   for (int64_t batch = first; batch < nbatches; batch += per_it) {
     const int64_t row0 = batch * R;
-    // y of the row this lane evaluates: asked for before the wait on the ring, so its latency hides behind it
+    // y of the row this lane evaluates was asked for one batch ago (as raw bits: converting an int64 at once would make
+    // the warp wait for the load right there -- a fifth of all stall samples in the first version); ask for the next one
     const int64_t myrow = row0 + (lane % R);
     const bool inb = myrow < n;
-    const double yv = inb ? load_y(a.y, a.ydt, myrow) : 0.0;
+    const long long ybits = ynext;
+    {
+      const int64_t nrow = myrow + per_it * R;
+      ynext = nrow < n ? reinterpret_cast<const long long*>(a.y)[nrow] : 0;
+    }
     // refill the stage this warp finished reading in the previous iteration
     if (lane == 0) {
       const int64_t ahead = batch + (NS - 1) * per_it;
@@ -326,6 +342,7 @@ k_oz_rows(const OzRowsArgs a) {
 #pragma unroll
     for (int r = 1; r < R; r++) if ((lane % R) == r) eta = part[r];
     eta += beta0;
+    const double yv = !inb ? 0.0 : (a.ydt == NB_F64 ? __longlong_as_double(ybits) : (double)ybits);
     LinkOut lo = a.skip_obj ? glm_link_noobj_rt(a.family, eta, yv) : glm_link_rt(a.family, eta, yv);
     if (!inb) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
     const double sw = sqrt(lo.wgt);
@@ -448,6 +465,8 @@ struct OzGemmArgs {
   int nranges;
   int lanes;                // pairs per group
   int32_t* part;            // [nranges][OZ_GROUPS][OZ_SLOTS][256][256]
+  int scheme;               // which product table
+  int debug;                // NUMS_B200_OZ_DEBUG: pair 0 prints the time from a stage's copies to its arrival
 };
 
 // Pair p works for group p % 4 on the row ranges p / 4, p / 4 + lanes, ...: the four pairs of a lane walk the same rows;
@@ -459,12 +478,13 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
   uint8_t* zero_tile = tiles + (size_t)(OZ_TILES - 1) * OZ_TILE;                      // the last tile stays zero
   __shared__ __align__(8) uint64_t full[OZ_MAX_STAGES], empty[OZ_MAX_STAGES], acc_full, acc_empty;
   __shared__ uint32_t tmem_base_s;
+  __shared__ long long dbg_issue[OZ_MAX_STAGES];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = oz_cluster_rank();
   const int pair = blockIdx.x >> 1;
   const int group = pair % OZ_GROUPS, lane_id = pair / OZ_GROUPS;
-  const int np = c_oz_nplanes[group];
-  const int nst = (OZ_TILES - 1) / np;               // pipeline stages of this group
+  const int np = c_oz_nplanes[a.scheme][group];
+  const int nst = (OZ_TILES - 1) / np < OZ_MAX_STAGES ? (OZ_TILES - 1) / np : OZ_MAX_STAGES;     // pipeline stages of this group
 
   for (int i = threadIdx.x; i < (int)(OZ_TILE / 16); i += blockDim.x) reinterpret_cast<uint4*>(zero_tile)[i] = make_uint4(0, 0, 0, 0);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // the tensor core reads it through the async proxy
@@ -500,12 +520,13 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
           oz_mbar_wait(&empty[st], ph);
           if (rank == 0) oz_mbar_expect_tx(&full[st], 2u * (uint32_t)np * OZ_TILE);
           else oz_mbar_arrive_remote(&full[st], 0);
+          if (a.debug) dbg_issue[st] = clock64();
           const uint32_t bar = lead_full0 + (uint32_t)st * 8u;
           const int c0 = (int)rank * OZ_HALF;
           const int c1 = (int)(r0 + (int64_t)ch * OZ_KC);
           for (int q = 0; q < np; q++) {
             const uint32_t dst = oz_smem(tiles + ((size_t)st * np + q) * OZ_TILE);
-            const int c2 = c_oz_planes[group][q];
+            const int c2 = c_oz_planes[a.scheme][group][q];
             asm volatile("cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
                          " [%0], [%1, {%3, %4, %5}], [%2];"
                          :: "r"(dst), "l"(&tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
@@ -517,39 +538,65 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (leader CTA, one thread)
     if (rank == 0 && lane == 0) {
-      // staged position of every plane of this group
-      int pos[OZ_S];
-      for (int p = 0; p < OZ_S; p++) pos[p] = 0;
-      for (int q = 0; q < np; q++) pos[c_oz_planes[group][q]] = q;
+      // Everything the issue loop needs sits in registers before it starts: per product the operands' offsets inside a stage
+      // (16-byte units), the accumulator's tensor-memory address and whether it is the first product into its slot.  One thread
+      // has 128 cycles per MMA to build two descriptors and issue; constant-memory and local-memory reads in that path (the
+      // first version indexed the tables per MMA) held the tensor pipe at ~55 %.
+      uint32_t a_off[3], b_off[3], dcol[3], first[3];
+      bool b_fixed[3], valid[3];
+      {
+        uint32_t seen = 0;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          const OzProduct pr = c_oz_products[a.scheme][group][k];
+          valid[k] = pr.slot >= 0;
+          int pa = 0, pb = 0;
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            if (q < np && c_oz_planes[a.scheme][group][q] == pr.pa) pa = q;
+            if (q < np && c_oz_planes[a.scheme][group][q] == pr.pb) pb = q;
+          }
+          a_off[k] = (uint32_t)pa * (OZ_TILE >> 4);
+          b_fixed[k] = pr.pb < 0;
+          b_off[k] = pr.pb < 0 ? (oz_smem(zero_tile) >> 4) : (uint32_t)pb * (OZ_TILE >> 4);
+          const int slot = valid[k] ? pr.slot : 0;
+          dcol[k] = tmem_base + (uint32_t)slot * 256u;
+          first[k] = ((seen >> slot) & 1u) ? 0u : 1u;
+          if (valid[k]) seen |= 1u << slot;
+        }
+      }
+      const uint64_t desc_hi = oz_desc(0);                       // everything but the start address
+      const uint32_t tiles_u = oz_smem(tiles) >> 4;
+      const uint32_t stage_u = (uint32_t)np * (OZ_TILE >> 4);
+      constexpr uint32_t KSTEP = (32 * OZ_HALF) >> 4;            // 32 rows of a tile, in 16-byte units
       int item = 0, st = 0;
       unsigned ph = 0;
+      long long dbg_lat = 0, dbg_wait = 0, dbg_n = 0, dbg_t0 = clock64();
       for (int range = lane_id; range < a.nranges; range += a.lanes, item++) {
         const int64_t r0 = (int64_t)range * a.range_rows;
         int64_t rem = a.n - r0;
         const int nch = (int)((rem < a.range_rows ? (rem + OZ_KC - 1) / OZ_KC : chunks_per_range));
         if (item > 0) oz_mbar_wait(&acc_empty, (unsigned)((item - 1) & 1));      // the epilogue has drained the accumulators
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        uint32_t started = 0;                 // bit s: slot s holds a partial sum of this item
         for (int ch = 0; ch < nch; ch++) {
+          const long long w0 = a.debug ? clock64() : 0;
           oz_mbar_wait(&full[st], ph);
+          if (a.debug) { const long long w1 = clock64(); dbg_wait += w1 - w0; dbg_lat += w1 - dbg_issue[st]; dbg_n++; }
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t stage_base = oz_smem(tiles + (size_t)st * np * OZ_TILE);
+          const uint32_t base_u = tiles_u + (uint32_t)st * stage_u;
 #pragma unroll
           for (int k = 0; k < 3; k++) {
-            const OzProduct pr = c_oz_products[group][k];
-            if (pr.slot < 0) continue;
-            const uint32_t abase = stage_base + (uint32_t)pos[pr.pa] * OZ_TILE;
-            const uint32_t bbase = pr.pb < 0 ? oz_smem(zero_tile) : stage_base + (uint32_t)pos[pr.pb] * OZ_TILE;
-            const uint32_t dcol = tmem_base + (uint32_t)pr.slot * 256u;
+            if (!valid[k]) continue;
+            const uint32_t au = base_u + a_off[k];
+            const uint32_t bu = b_fixed[k] ? b_off[k] : base_u + b_off[k];
 #pragma unroll
             for (int ks = 0; ks < OZ_KC / 32; ks++) {
-              const uint64_t ad = oz_desc(abase + ks * 32 * OZ_HALF);
-              const uint64_t bd = oz_desc(bbase + ks * 32 * OZ_HALF);
-              const uint32_t acc = (started >> pr.slot) & 1u;
+              const uint64_t ad = desc_hi | (uint64_t)((au + ks * KSTEP) & 0x3fffu);
+              const uint64_t bd = desc_hi | (uint64_t)((bu + ks * KSTEP) & 0x3fffu);
+              const uint32_t acc = (ch > 0 || ks > 0 || !first[k]) ? 1u : 0u;
               asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                            "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}"
-                           :: "r"(dcol), "l"(ad), "l"(bd), "r"(OZ_IDESC), "r"(acc), "r"(0u) : "memory");
-              started |= 1u << pr.slot;
+                           :: "r"(dcol[k]), "l"(ad), "l"(bd), "r"(OZ_IDESC), "r"(acc), "r"(0u) : "memory");
             }
           }
           // the stage may be refilled (both CTAs) once these MMAs have read it
@@ -560,6 +607,10 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
         asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                      :: "r"(oz_smem(&acc_full)), "h"((uint16_t)3) : "memory");
       }
+      if (a.debug && pair < 4 && dbg_n > 0)
+        printf("k_oz_gemm pair %d (group %d, %d planes, %d stages): %lld stages, %.0f clk per stage, copy->arrival %.0f clk, "
+               "issuer waited %.0f clk per stage\n", pair, group, np, nst, dbg_n, (double)(clock64() - dbg_t0) / dbg_n,
+               (double)dbg_lat / dbg_n, (double)dbg_wait / dbg_n);
     }
   } else {
     // ------------------------------------------------------------ epilogue warps 2..5 (both CTAs)
@@ -626,6 +677,7 @@ struct OzFinishArgs {
   const OzPrep* prep;
   int ew;
   const int* flag;
+  int scheme;
   double* out;              // d x d corner, row stride ldc
 };
 
@@ -645,9 +697,11 @@ k_oz_finish(const OzFinishArgs a) {
 #pragma unroll
       for (int s = 0; s < OZ_SLOTS; s++) {
         const long long* t = a.sums + ((size_t)g * OZ_SLOTS + s) * 65536;
+        const int level = c_oz_slot_level[a.scheme][g][s];
+        if (level < 0) continue;                 // a slot the scheme does not use holds whatever tensor memory held
         long long v = t[i * 256 + j];
-        if (c_oz_slot_off[g][s]) v += t[j * 256 + i];
-        lev[c_oz_slot_level[g][s]] += v;
+        if (c_oz_slot_off[a.scheme][g][s]) v += t[j * 256 + i];
+        lev[level] += v;
       }
     // sum_L lev[L] 256^(8-L), smallest terms first; every term is exact in double
     double acc = 0.0;
@@ -737,7 +791,7 @@ static OzEncodeFn oz_encode_fn() {
 // pass B then works on the planes the previous call left in the scratch).
 int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                  const double* beta, int skip_obj, const void* prep, double* stats, double* parts, int max_parts,
-                 int* nparts, void* scratch, size_t scratch_bytes, int phases, cudaStream_t st) {
+                 int* nparts, void* scratch, size_t scratch_bytes, int phases, int scheme, cudaStream_t st) {
   const OzPlan p = oz_plan(device, n);
   NB_REQUIRE(scratch != nullptr && scratch_bytes >= p.total, "int8 Hessian: scratch too small (%zu < %zu)",
              scratch_bytes, p.total);
@@ -792,7 +846,8 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       NB_REQUIRE(cr == CUDA_SUCCESS, "int8 Hessian: cuTensorMapEncodeTiled failed (%d)", (int)cr);
       OzGemmArgs ga;
-      ga.n = cn; ga.range_rows = p.range_rows; ga.nranges = cranges; ga.lanes = p.lanes;
+      ga.n = cn; ga.range_rows = p.range_rows; ga.nranges = cranges; ga.lanes = p.lanes; ga.scheme = scheme;
+      ga.debug = NB_ENV_FLAG("NUMS_B200_OZ_DEBUG") ? 1 : 0;
       ga.part = part + (size_t)ranges_done * OZ_GROUPS * OZ_SLOTS * 65536;
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3((unsigned)(2 * p.pairs));
@@ -814,7 +869,7 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
   NB_LAUNCH_CHECK();
   OzFinishArgs fa;
   fa.d = d; fa.ldc = d + 1; fa.sums = sums; fa.prep = (const OzPrep*)prep; fa.ew = ew;
-  fa.flag = flag; fa.out = stats;
+  fa.flag = flag; fa.out = stats; fa.scheme = scheme;
   const int64_t blocks = (d * (d + 1) / 2 + 255) / 256;
   k_oz_finish<<<(unsigned)blocks, 256, 0, st>>>(fa);
   NB_LAUNCH_CHECK();

@@ -3,6 +3,7 @@ reference's own fusion uses: nums/experimental/optimizer/graph.py:801-810, invok
 
 Each takes/returns DeviceBlocks and calls one C-ABI entry point of libnumsb200.so.
 """
+import math
 import os
 
 import numpy as np
@@ -15,6 +16,7 @@ from .device import DeviceBlock
 
 
 NB_GLM_INT8_HESSIAN = 4
+NB_GLM_INT8_NO_LEVEL5 = 32
 _HESSIAN_MODES = ("fp64", "int8", "int8!")
 
 
@@ -34,6 +36,16 @@ def int8_hessian_applies(x, family):
 
 
 INT8_MAX_RANGE_LOG2 = 5     # largest entry of a column at most 32x its r.m.s.: fixed-point error of H below 1e-10
+
+
+def int8_flags(found, rows):
+    """Mode bits of the int8 Hessian for a prepared block of `rows` rows: the level-5 digit products are left out when their
+    contribution (zero-mean, ~ 2^(2r - 38.6) / sqrt(n) relative to H, with a factor 5 for the largest of 65536 entries) is
+    below 1e-11 -- a tenth of the parity bar."""
+    flags = NB_GLM_INT8_HESSIAN
+    if rows > 0 and 5.0 * 2.0 ** (2 * found.range_log2 - 38.6) / math.sqrt(rows) <= 1e-11:
+        flags |= NB_GLM_INT8_NO_LEVEL5
+    return flags
 
 
 class BlockPrep:
@@ -90,7 +102,7 @@ def glm_stats(x, y, beta, family, want_hess, need_obj=True, hessian=None):
         found = glm_prepare(x)
         if found.usable or choice == "int8!":     # "int8!": whatever the dynamic range of the columns (tests)
             prep = found.buf.data_ptr()
-            mode |= NB_GLM_INT8_HESSIAN
+            mode |= int8_flags(found, n)
     sc = dv.scratch(lib.nb_glm_scratch_bytes(dev, n, d, mode), dev)
     _lib.check(lib.nb_glm_stats_prepared(dev, hl.FAMILY_CODE[family], x.ptr, n, d, x.strides[0], y.ptr, y.code,
                                          beta.ptr, mode, prep, out.ptr, sc.data_ptr(), sc.numel(),
@@ -156,6 +168,7 @@ def glm_newton_fit(family, beta, l2vec, tol, max_iter, hessian, *blocks):
     l2 = dv.contiguous(dv.to_device(l2vec, dev)) if l2vec is not None else None
     mode = 3                                                            # NB_GLM_HESS_NO_OBJECTIVE
     preps = [None] * nb
+    flags = []
     choice = hessian or default_hessian()
     if choice in ("int8", "int8!"):
         for i, x in enumerate(xs):
@@ -163,8 +176,11 @@ def glm_newton_fit(family, beta, l2vec, tol, max_iter, hessian, *blocks):
                 found = glm_prepare(x)
                 if found.usable or choice == "int8!":
                     preps[i] = found.buf.data_ptr()
-        if any(pp is not None for pp in preps):
+                    flags.append(int8_flags(found, x.shape[0]))
+        if flags:
             mode |= NB_GLM_INT8_HESSIAN
+            if all(f & NB_GLM_INT8_NO_LEVEL5 for f in flags):
+                mode |= NB_GLM_INT8_NO_LEVEL5
     import ctypes as C
     VP, I64 = C.c_void_p * nb, C.c_int64 * nb
     rows = [x.shape[0] for x in xs]
