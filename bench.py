@@ -54,6 +54,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--no-strong", action="store_true")
+    ap.add_argument("--config", default="newton256", choices=["newton256", "lbfgs1024"],
+                    help="newton256: the headline (BASELINE configs[3]); lbfgs1024: configs[4], Linear / Poisson lbfgs on a "
+                         "1.25e7 x 1024 shard per GPU (102 GB resident), 10 iterations")
     return ap.parse_args()
 
 
@@ -345,7 +348,94 @@ def extras_single_gpu(torch, app, dv, fused, lib, _lib, local, hbm_peak, fp64_pe
     return out
 
 
+def run_lbfgs1024(args, result):
+    """BASELINE configs[4]: LinearRegression / PoissonRegression, solver lbfgs, 10^8 x 1024 float64 at 8 GPUs = a
+    1.25e7 x 1024 shard per rank (weak scaling for fewer ranks).  Every evaluation is one fused gradient + objective pass
+    and one all-reduce of p + 1 doubles (packed with the unused Hessian slot); the optimiser state lives on the device."""
+    import torch
+    import torch.distributed as dist
+    from nums_b200 import device as dv, fused
+    from nums_b200.app import make_app, set_instance
+    from nums_b200.blockarray import BlockArray
+    from nums_b200 import glms
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    app = set_instance(make_app(device_ids=[local]))
+    km = app.km
+    n, d, iters = args.rows, 1024, 10
+    rng = np.random.Generator(np.random.PCG64(1337).jumped(rank))
+    chunk = 1 << 16
+    Xc = rng.normal(0.0, 1.0, chunk * d).reshape(chunk, d) / np.sqrt(d)
+    w_true = np.random.Generator(np.random.PCG64(7)).normal(0.0, 1.0, d)
+    src = dv.from_numpy(Xc, local)
+    X = dv.empty((n, d), np.float64, local)
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        dv.copy_into(X.t[lo:hi], src.t[: hi - lo])
+    XB = BlockArray.from_oid(X, (n, d), np.float64, km)
+    passes = [0]
+    inner = km.backend._remote_functions["glm_stats"] if "glm_stats" in km.backend._remote_functions else None
+    fused.register(km)
+    inner = km.backend._remote_functions["glm_stats"]
+
+    def counted(*a, **k):
+        passes[0] += 1
+        return inner(*a, **k)
+    km.backend._remote_functions["glm_stats"] = counted
+    out = {}
+    for name, cls, yc in (("linear", glms.LinearRegression, Xc @ w_true + 0.1 * rng.normal(0.0, 1.0, chunk)),
+                          ("poisson", glms.PoissonRegression, np.exp(Xc @ w_true))):      # tests/models/test_glms.py:245
+        ysrc = dv.from_numpy(yc, local)
+        y = dv.empty((n,), np.float64, local)
+        for lo in range(0, n, chunk):
+            hi = min(n, lo + chunk)
+            dv.copy_into(y.t[lo:hi], ysrc.t[: hi - lo])
+        yB = BlockArray.from_oid(y, (n,), np.float64, km)
+        for rep in range(2):            # the first fit warms allocator and caches
+            passes[0] = 0
+            m = cls(app=app, solver="lbfgs", tol=0.0, max_iter=iters)
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            m.fit(XB, yB)
+            coef = m._beta.get()
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        out[name] = {"iterations": m.n_iter_, "passes": passes[0], "seconds": dt, "ms_per_pass_incl_host": dt * 1e3 / passes[0],
+                     "gbs": world * passes[0] * n * (8 * d + 8) / dt / 1e9, "coef_checksum": float(np.sum(np.abs(coef)))}
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm = float(peaks.get("hbm_gbs", 6650.0))
+        lin = out["linear"]
+        result["line"] = {
+            "metric": "L-BFGS evaluation HBM GB/s (LinearRegression lbfgs, algorithmic bytes n*(8d+8) per pass, host overhead included)",
+            "value": lin["gbs"], "unit": "GB/s", "n_gpus": world, "steps": iters, "warmup": 1,
+            "ms_per_step": lin["seconds"] * 1e3 / iters, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic (reference block-RNG chunk of %d rows tiled over each shard)" % chunk,
+            "config": {"workload": "LinearRegression / PoissonRegression lbfgs, %dx1024 float64 per GPU (BASELINE configs[4]: "
+                                   "10^8x1024 = 8 such shards)" % n, "rows_per_gpu": n, "d": d, "max_iter": iters},
+            "frac_of_hbm_per_gpu": lin["gbs"] / world / hbm, "linear": lin, "poisson": out["poisson"], "gpu_launches": 2 * lin["passes"]}
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def run_ours(args, result):
+    if args.config == "lbfgs1024":
+        return run_lbfgs1024(args, result)
     import torch
     import torch.distributed as dist
     from nums_b200 import _lib, device as dv, fused
