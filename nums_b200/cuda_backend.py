@@ -11,6 +11,7 @@ synchronisation point, like `ray.get`.
 When the real `nums` package is importable this class derives from its `Backend`; otherwise from a
 local stand-in with the same 12 methods, so the plug-in also runs where NumS itself is absent.
 """
+import os
 import sys
 
 import numpy as np
@@ -27,6 +28,9 @@ except Exception:  # NumS not installed (e.g. on the GPU box)
 
     class _BackendBase:
         """Stand-in with the interface of nums.core.backends.base.Backend."""
+
+
+_NVTX = bool(os.environ.get("NUMS_B200_NVTX"))
 
 
 class HostObject:
@@ -128,7 +132,15 @@ class CudaBackend(_BackendBase):
         args = [self._localise(a, target) for a in args]
         kwargs = {k: self._localise(v, target) for k, v in kwargs.items()}
         with torch.cuda.device(target):
-            return self._remote_functions[name](*args, **kwargs)
+            if not _NVTX:
+                return self._remote_functions[name](*args, **kwargs)
+            # NUMS_B200_NVTX=1: one NVTX range per block operation (the tracing hook of SURVEY.md section 5: nsys / ncu
+            # --nvtx timelines then show the reference's operation names above the kernels they launch)
+            torch.cuda.nvtx.range_push("nums:%s@gpu%d" % (name, target))
+            try:
+                return self._remote_functions[name](*args, **kwargs)
+            finally:
+                torch.cuda.nvtx.range_pop()
 
     @staticmethod
     def _localise(value, target):

@@ -11,7 +11,9 @@ Two execution modes, same results:
   fused=False the reference algorithm op by op through the generic block kernels (X@beta, exp, X^T r,
               s*X, X^T(sX), inv ...), exactly as glms.py:457-499/660-676 schedules it.  Used to
               cross-check the generic kernels end to end.
-Quirks kept on purpose: "newton-cg" is plain Newton with an explicit inverse (glms.py:179-182,673);
+Quirks kept on purpose: a non-finite gradient or Hessian ends newton() with beta = NaN, as the reference's loop does
+(np.linalg.inv of a NaN matrix returns NaNs, and NaN <= tol never stops it), not with LinAlgError; "newton-cg" is plain
+Newton with an explicit inverse (glms.py:179-182,673);
 the convergence test uses the gradient from before the update (:674); the objective penalty is the
 un-squared norm over all of beta (:242-252) while the gradient penalty skips the intercept (:254-264).
 """

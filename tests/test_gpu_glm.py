@@ -554,3 +554,20 @@ def test_one_process_two_devices(monkeypatch):
         assert np.max(np.abs(got - want)) < COEF_TOL and m.n_iter_ == it
     x = app2.array(rng.random(200_000), block_shape=(100_000,))
     assert rel_err((x.T @ x).get(), float(x.get() @ x.get())) < STAT_TOL
+
+
+@pytest.mark.parametrize("d", [2, 40, 256])
+def test_newton_with_a_nan_in_x_ends_like_the_reference(app, d):
+    """A NaN in X makes g and H non-finite.  np.linalg.inv returns NaNs without raising, `max|g| <= tol` is never true for
+    a NaN, so the reference's newton() runs to max_iter and returns beta = NaN (glms.py:660-676).  Same outcome here — not
+    a LinAlgError("Singular matrix") — for the small-p solver, the Cholesky / inverse path and the int8 Hessian (whose
+    prepare step flags the block and sends it to FP64)."""
+    from nums_b200.glms import LogisticRegression
+    rng = np.random.default_rng(d)
+    n = 4000
+    X = rng.standard_normal((n, d))
+    X[123, d // 2] = np.nan
+    y = (rng.random(n) < 0.5).astype(np.int64)
+    m = LogisticRegression(app=app, solver="newton", penalty="l2", C=10, max_iter=5)
+    m.fit(app.array(X, block_shape=(n // 2, d)), app.array(y, block_shape=(n // 2,)))
+    assert np.all(np.isnan(m._beta.get())) and np.isnan(float(m._beta0.get()))

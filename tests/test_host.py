@@ -227,3 +227,19 @@ def test_reference_layers_drive_the_plugin_host_logic():
                               capture_output=True, text=True, timeout=600)
         assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
         assert proc.stdout.count("\nok") + proc.stdout.startswith("ok") >= 14
+
+
+def test_oracle_ref_is_an_unmodified_copy_of_the_reference():
+    """oracle/_ref/nums must be byte-identical to /root/reference/nums (build container only): the boundary tests and the
+    timed CPU arm claim to run the reference itself."""
+    import hashlib
+    import json
+    from oracle import make_ref, refharness
+    if not refharness.present() or not os.path.isdir(os.path.join(REF, "nums")):
+        pytest.skip("needs both oracle/_ref and /root/reference")
+    manifest = json.load(open(os.path.join(make_ref.OUT, "MANIFEST.json")))["files"]
+    assert len(manifest) > 50
+    for rel, digest in manifest.items():
+        here = hashlib.sha256(open(os.path.join(make_ref.OUT, rel), "rb").read()).hexdigest()
+        there = hashlib.sha256(open(os.path.join(REF, rel), "rb").read()).hexdigest()
+        assert here == there == digest, rel
