@@ -218,6 +218,29 @@ def event_ms(torch, fn, reps, warm=2):
     return e0.elapsed_time(e1) / reps
 
 
+def event_ms_alternating(torch, fns, reps, warm=2):
+    """Mean device time of each fn when they run alternately (f0 f1 f0 f1 ...), every call between its own pair of CUDA
+    events: the kernels of one step, at the clocks and power state of the step loop.  (A loop over ONE of them runs in
+    another power regime: the board is at its power cap in steady state.)"""
+    for _ in range(warm):
+        for fn in fns:
+            fn()
+    torch.cuda.synchronize()
+    marks = []
+    for _ in range(reps):
+        for i, fn in enumerate(fns):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            marks.append((i, e0, e1))
+    torch.cuda.synchronize()
+    out = [0.0] * len(fns)
+    for i, e0, e1 in marks:
+        out[i] += e0.elapsed_time(e1) / reps
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
@@ -534,8 +557,8 @@ def run_ours(args, result):
         sc8 = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 3 | INT8), local)
         pp = prep.buf.data_ptr()
         parts["stats_int8_ms"] = event_ms(torch, lambda: stats_call(3 | INT8, pp, sc8), reps)
-        parts["rows_ms"] = event_ms(torch, lambda: stats_call(3 | INT8 | ROWS, pp, sc8), reps)
-        parts["products_ms"] = event_ms(torch, lambda: stats_call(3 | INT8 | PROD, pp, sc8), reps)
+        parts["rows_ms"], parts["products_ms"] = event_ms_alternating(
+            torch, [lambda: stats_call(3 | INT8 | ROWS, pp, sc8), lambda: stats_call(3 | INT8 | PROD, pp, sc8)], reps)
         del sc8
         torch.cuda.empty_cache()
     sc64 = dv.scratch(lib.nb_glm_scratch_bytes(local, n, d, 3), local)
@@ -701,20 +724,23 @@ def run_ours(args, result):
     if int8_used:
         dominant = "rows" if parts["rows_ms"] >= parts["products_ms"] else "products"
         roof_ms = parts["rows_ms"]
+        i8flags = fused.int8_flags(prep, n)
+        nplanes = 4 if (i8flags & fused.NB_GLM_INT8_FOUR_PLANES) else 5
+        moved = n * d * (8 + nplanes) + 8 * n
         roofline = {
             "bound": "hbm",
-            "kernel": "k_oz_rows (pass A of the int8 Hessian: link, gradient, u and the five int8 digit planes; reads X "
-                      "once, writes 5 bytes per element) + k_glm_rows_finish, timed alone (NB_GLM_INT8_ROWS_ONLY) with CUDA "
-                      "events on its stream",
+            "kernel": "k_oz_rows (pass A of the int8 Hessian: link, gradient, u and the %d int8 digit planes; reads X "
+                      "once, writes %d bytes per element) + k_glm_rows_finish, timed alone (NB_GLM_INT8_ROWS_ONLY) with CUDA "
+                      "events on its stream, alternating with pass B as in a step" % (nplanes, nplanes),
             "achieved": gram_bytes / (roof_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
             "frac": gram_bytes / (roof_ms * 1e-3) / 1e9 / hbm_peak, "traffic": traffic.get("k_oz_rows_dram_bytes"),
             "peak_source": peak_src, "ms_per_launch": roof_ms, "algorithmic_bytes_per_launch": gram_bytes,
-            "moved_bytes_per_launch": n * d * 13 + 8 * n,
-            "frac_of_moved_bytes": (n * d * 13 + 8 * n) / (roof_ms * 1e-3) / 1e9 / hbm_peak,
+            "moved_bytes_per_launch": moved,
+            "frac_of_moved_bytes": moved / (roof_ms * 1e-3) / 1e9 / hbm_peak,
             "dominant_of_step": dominant,
-            "note": "algorithmic bytes = n*(8d+8) (X and y once); the kernel also writes the digit planes (5 B per element), "
-                    "so it moves 13/8 of that: frac_of_moved_bytes is its HBM efficiency"}
-        nprod = 9 if (fused.int8_flags(prep, n) & fused.NB_GLM_INT8_NO_LEVEL5) else 11
+            "note": "algorithmic bytes = n*(8d+8) (X and y once); the kernel also writes the digit planes (%d B per element), "
+                    "so it moves %d/8 of that: frac_of_moved_bytes is its HBM efficiency" % (nplanes, 8 + nplanes)}
+        nprod = 8 if nplanes == 4 else (9 if (i8flags & fused.NB_GLM_INT8_NO_LEVEL5) else 11)
         int8_ops = nprod * 2.0 * 256 * 256 * n
         tensor = {
             "bound": "tensor", "kernel": "k_oz_gemm (pass B: %d exact int8 plane products," % nprod + " tcgen05.mma kind::i8 cta_group::2, "

@@ -326,6 +326,11 @@ int nb_glm_stats(int device, int family, const double* x_d, int64_t n, int64_t d
  * relative contribution to H is ~ 2^(2 r - 38.6) / sqrt(n) (r = range_log2 of nb_glm_prepare, n rows): the caller sets this
  * when that is far below its tolerance (nums_b200.fused: <= 1e-11), which takes a quarter off the operand traffic */
 #define NB_GLM_INT8_NO_LEVEL5 32
+/* with NB_GLM_INT8_HESSIAN: FOUR digit planes (x sqrt(w) rounded to 31 bits per column scale) and eight plane products.
+ * The rounding error of H grows to ~ 2^(r - 31) / sqrt(n) relative to sqrt(H_ii H_jj) (random sign over n rows): for
+ * blocks of millions of rows that is still below 1e-11 (nums_b200.fused sets the flag only then), and the pass writes and
+ * reads a fifth fewer plane bytes and runs 8 instead of 9 products on fully used accumulators */
+#define NB_GLM_INT8_FOUR_PLANES 64
 #define NB_GLM_INT8_ROWS_ONLY 8
 #define NB_GLM_INT8_PRODUCTS_ONLY 16
 size_t nb_glm_prep_bytes(int64_t d);

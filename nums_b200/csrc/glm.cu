@@ -535,7 +535,7 @@ int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, 
   const int skip_obj = (want_hess & 2) ? 1 : 0;      // NB_GLM_NO_OBJECTIVE
   const bool int8_hess = (want_hess & NB_GLM_INT8_HESSIAN) != 0;
   const int oz_phases = (want_hess & NB_GLM_INT8_ROWS_ONLY) ? 1 : ((want_hess & NB_GLM_INT8_PRODUCTS_ONLY) ? 2 : 3);
-  const int oz_scheme = (want_hess & NB_GLM_INT8_NO_LEVEL5) ? 1 : 0;
+  const int oz_scheme = (want_hess & NB_GLM_INT8_FOUR_PLANES) ? 2 : ((want_hess & NB_GLM_INT8_NO_LEVEL5) ? 1 : 0);
   want_hess &= 1;
   NB_REQUIRE(!int8_hess || prep_d != nullptr, "nb_glm_stats: NB_GLM_INT8_HESSIAN needs the block's nb_glm_prepare output");
   GlmLayout L = glm_layout(device, n, d, want_hess, int8_hess);
@@ -675,7 +675,7 @@ int nb_glm_newton_fit(int device, int family, int nblocks, const double* const* 
   for (int it = 0; it < max_iter; it++) {
     for (int b = 0; b < nblocks; b++) {
       const void* prep = preps ? preps[b] : nullptr;
-      const int mode = prep ? want_hess_flags : (want_hess_flags & ~(NB_GLM_INT8_HESSIAN | NB_GLM_INT8_NO_LEVEL5));
+      const int mode = prep ? want_hess_flags : (want_hess_flags & ~(NB_GLM_INT8_HESSIAN | NB_GLM_INT8_NO_LEVEL5 | NB_GLM_INT8_FOUR_PLANES));
       int rc = nb_glm_stats_prepared(device, family, x_blocks[b], rows[b], d, ldx[b], y_blocks[b], ydt, cur, mode, prep,
                                      buf(b), gsc, gsc_bytes, stream);
       if (rc) return rc;

@@ -39,16 +39,17 @@ namespace nb {
 constexpr int OZ_S = 5;                 // digit planes
 constexpr int OZ_COLS = 256;            // plane width (columns of X, zero padded)
 constexpr int OZ_HALF = 128;
-constexpr int OZ_KC = 64;               // rows per pipeline stage
-constexpr int OZ_TILES = 26;              // 8 KB tiles of shared memory: a group with np planes runs OZ_TILES / np stages
+constexpr int OZ_KC = 64;               // rows per pipeline stage (schemes 0, 1; scheme 2 runs 128-row stages)
+constexpr int OZ_KC_MAX = 128;
+constexpr int OZ_SMEM_TILES = 26 * 64 * OZ_HALF;   // 208 KB of plane tiles per CTA: (tiles - 1) / np stages, the last tile stays zero
 constexpr int OZ_MAX_STAGES = 12;
 constexpr int OZ_MAX_RANGE = 32768;     // rows per accumulation (int32 headroom)
 constexpr int OZ_GROUPS = 4;
 constexpr int OZ_SLOTS = 2;
-constexpr uint32_t OZ_TILE = OZ_KC * OZ_HALF;           // 8 KB: one plane, one column half, one stage
 constexpr int OZ_ROWS_THREADS = 256;
 constexpr int OZ_R = 4;                 // rows per warp step in pass A
-constexpr int OZ_VBITS = 38;            // |v| < 2^38
+// |v| < 2^vbits: five planes carry 39-bit values, four planes 31-bit values
+__host__ __device__ constexpr int oz_vbits(int nplanes) { return nplanes == 5 ? 38 : 30; }
 
 // products of each group: {slot, plane of A, plane of B}; planes the group stages.  Levels 0..5 (11 products, 8 slots:
 // the first dropped terms, level 6, are 2^-48 of the column scale squared).
@@ -62,7 +63,7 @@ struct OzProduct { int slot, pa, pb; };
 // stage, so the four pairs of a lane advance at the same pace and stay close: the pair that asks for a tile first pays the
 // trip to HBM, the others find it in L2.  Group 3 has only two useful products on three planes; its third is plane 3 against a
 // tile of zeros (pb = -1, adds nothing) -- the idle tensor time buys the lock step (DRAM re-reads 2.1x -> 1.66x).
-constexpr int OZ_SCHEMES = 2;
+constexpr int OZ_SCHEMES = 3;
 __constant__ OzProduct c_oz_products[OZ_SCHEMES][OZ_GROUPS][3] = {
     {{{0, 0, 3}, {0, 1, 2}, {1, 0, 0}},        // level 3 | level 0
      {{0, 0, 4}, {0, 1, 3}, {1, 0, 1}},        // level 4, pairs p < p' | level 1
@@ -72,14 +73,24 @@ __constant__ OzProduct c_oz_products[OZ_SCHEMES][OZ_GROUPS][3] = {
      {{0, 0, 4}, {0, 1, 3}, {1, 0, 1}},        // level 4, pairs p < p' | level 1
      {{0, 2, 2}, {1, 1, 1}, {-1, 0, 0}},       // level 4, (2,2) | level 2, (1,1)
      {{0, 0, 2}, {-1, 0, 0}, {-1, 0, 0}}},     // level 2, (0,2) | (slot 1 unused)
+    // scheme 2: FOUR planes (31-bit values), levels 0..4: eight products, two per group, every accumulator slot in use
+    {{{0, 0, 3}, {1, 0, 0}, {-1, 0, 0}},       // level 3, (0,3) | level 0
+     {{0, 1, 2}, {1, 0, 1}, {-1, 0, 0}},       // level 3, (1,2) | level 1
+     {{0, 1, 3}, {1, 2, 2}, {-1, 0, 0}},       // level 4, (1,3) | level 4, (2,2)
+     {{0, 0, 2}, {1, 1, 1}, {-1, 0, 0}}},      // level 2, (0,2) | level 2, (1,1)
 };
-__constant__ int c_oz_nplanes[OZ_SCHEMES][OZ_GROUPS] = {{4, 4, 4, 4}, {4, 4, 2, 2}};
+__constant__ int c_oz_nplanes[OZ_SCHEMES][OZ_GROUPS] = {{4, 4, 4, 4}, {4, 4, 2, 2}, {2, 3, 3, 3}};
 __constant__ int c_oz_planes[OZ_SCHEMES][OZ_GROUPS][4] = {{{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 3, 4}, {0, 1, 2, 3}},
-                                                          {{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 0, 0}, {0, 2, 0, 0}}};
+                                                          {{0, 1, 2, 3}, {0, 1, 3, 4}, {1, 2, 0, 0}, {0, 2, 0, 0}},
+                                                          {{0, 3, 0, 0}, {0, 1, 2, 0}, {1, 2, 3, 0}, {0, 1, 2, 0}}};
 // slot (group, s) -> level (-1: unused) and kind (1 = pairs p < p': enters as P + P^T; 0 = p == p')
 constexpr int OZ_LEVELS = 6;
-__constant__ int c_oz_slot_level[OZ_SCHEMES][OZ_GROUPS][OZ_SLOTS] = {{{3, 0}, {4, 1}, {5, 4}, {2, 2}}, {{3, 0}, {4, 1}, {4, 2}, {2, -1}}};
-__constant__ int c_oz_slot_off[OZ_SCHEMES][OZ_GROUPS][OZ_SLOTS] = {{{1, 0}, {1, 1}, {1, 0}, {1, 0}}, {{1, 0}, {1, 1}, {0, 0}, {1, 0}}};
+__constant__ int c_oz_slot_level[OZ_SCHEMES][OZ_GROUPS][OZ_SLOTS] = {{{3, 0}, {4, 1}, {5, 4}, {2, 2}}, {{3, 0}, {4, 1}, {4, 2}, {2, -1}},
+                                                                     {{3, 0}, {3, 1}, {4, 4}, {2, 2}}};
+__constant__ int c_oz_slot_off[OZ_SCHEMES][OZ_GROUPS][OZ_SLOTS] = {{{1, 0}, {1, 1}, {1, 0}, {1, 0}}, {{1, 0}, {1, 1}, {0, 0}, {1, 0}},
+                                                                   {{1, 0}, {1, 1}, {1, 0}, {1, 0}}};
+static const int h_oz_scheme_planes[OZ_SCHEMES] = {5, 5, 4};      // digit planes of each scheme
+static const int h_oz_scheme_kc[OZ_SCHEMES] = {64, 64, 128};        // rows per pipeline stage
 
 struct OzPrep {               // nb_glm_prepare output (device memory)
   int32_t colexp[OZ_COLS];    // max|x[:, i]| < 2^colexp[i];  INT32_MIN for an all-zero column
@@ -188,6 +199,7 @@ struct OzRowsArgs {
   int8_t* planes; int64_t plane_stride;     // plane p at planes + p * plane_stride, row k at + k * 256
   double* partials;             // [gridDim.x][2*d + 3]  (layout of k_glm_rows, summed by k_glm_rows_finish)
   int* flag;                    // set when a value leaves the 39-bit range
+  uint32_t seed;                // four planes: seed of the rounding dither (the chunk's first row)
 };
 
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
@@ -223,6 +235,7 @@ __device__ __forceinline__ void oz_rows_fetch(const OzRowsArgs& a, int64_t batch
 // keeps OZ_ROWS_STAGES batches in flight as bulk copies into its own shared-memory ring (lane 0 issues the copy for batch
 // i + STAGES - 1 before the warp starts on batch i); no producer warp and no "empty" barriers are needed because the
 // warp that refills a stage is the one that has just finished reading it.
+template <int NP>
 __global__ void __launch_bounds__(OZ_ROWS_THREADS, 1)
 k_oz_rows(const OzRowsArgs a) {
   constexpr int NW = OZ_ROWS_THREADS / 32;
@@ -248,20 +261,30 @@ k_oz_rows(const OzRowsArgs a) {
     const int col = (e < 4 ? cA : cB) + (e & 3);
     bet[e] = col < d ? a.beta[col] : 0.0;
     const int ce = a.prep->colexp[col];
-    // v = x sqrt(w) 2^q with q = VBITS - colexp - ew, so that |v| < 2^VBITS
-    int q = OZ_VBITS - ce - a.ew;
+    // v = x sqrt(w) 2^q with q = 38 - colexp - ew, so that |v| < 2^38 (four planes drop the lowest byte after a dither)
+    int q = oz_vbits(5) - ce - a.ew;
     cs[e] = (col < d && ce != INT32_MIN && q < 1000 && q > -1000) ? scalbn(1.0, q) : 0.0;
   }
   const double beta0 = a.beta[d];
   // 1.5 * 2^52 + sum_s 128 * 256^s: after fma(x, scale, MAGIC) the low 40 mantissa bits are v + bias, i.e. the
   // bytes d_s + 128 of the balanced base-256 digits of v (round to nearest even comes with the fma)
-  const double MAGIC = 6755399441055744.0 + 551911719040.0;
+  // Four planes: the same 39-bit value, but the lowest byte carries no bias and receives a uniform 8-bit dither; the four
+  // upper bytes are then floor((v + u) / 256) + bias, a rounding of v / 256 whose error has zero mean whatever v is.
+  const double MAGIC = 6755399441055744.0 + (NP == 5 ? 551911719040.0 : 551911718912.0);
+  constexpr uint32_t HI_OK = 0x43380000u, HI_MASK = 0xffffff00u;
+  constexpr uint32_t DITHER_LO = 0x80808000u;        // low word of MAGIC (four planes) without the dither byte
 
   double g[8], u[8];
 #pragma unroll
   for (int e = 0; e < 8; e++) { g[e] = 0.0; u[e] = 0.0; }
   double gi = 0.0, ui = 0.0, ob = 0.0;
   uint32_t bad = 0;
+  // Four planes keep 31 bits of x sqrt(w), and the 1e-10 bar on H then rests on the rounding errors of the n rows
+  // cancelling (~ 1 / sqrt(n)).  Round-to-nearest errors do not cancel over REPEATED rows (one-hot data, tiled test
+  // matrices): the same row rounds the same way every time.  The dither byte is hash(row) ^ (a constant per column): a
+  // given column sees independent uniform dithers down the rows, so its rounding errors are zero-mean and independent
+  // of the data.  It depends on the row's position only: the same block gives the same bits.
+  const uint32_t lane_key = ((uint32_t)lane * 0x9E3779B1u) >> 24;
 
   const int64_t nbatches = (n + R - 1) / R;
   const int64_t per_it = (int64_t)gridDim.x * NW;
@@ -278,9 +301,9 @@ k_oz_rows(const OzRowsArgs a) {
   if (first < nbatches && first * R + (lane % R) < n) ynext = reinterpret_cast<const long long*>(a.y)[first * R + (lane % R)];
   // this lane's byte position in every plane for the first row of the batch: advanced once per batch, so that the forty
   // plane stores of a batch need no address arithmetic beyond constant offsets
-  int8_t* pl[OZ_S];
+  int8_t* pl[NP];
 #pragma unroll
-  for (int p = 0; p < OZ_S; p++) pl[p] = a.planes + p * a.plane_stride + first * R * OZ_COLS + cA;
+  for (int p = 0; p < NP; p++) pl[p] = a.planes + p * a.plane_stride + first * R * OZ_COLS + cA;
   const int64_t pl_step = per_it * R * OZ_COLS;
   for (int64_t batch = first; batch < nbatches; batch += per_it) {
     const int64_t row0 = batch * R;
@@ -346,6 +369,12 @@ k_oz_rows(const OzRowsArgs a) {
     LinkOut lo = a.skip_obj ? glm_link_noobj_rt(a.family, eta, yv) : glm_link_rt(a.family, eta, yv);
     if (!inb) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
     const double sw = sqrt(lo.wgt);
+    uint32_t rowkey = 0;
+    if constexpr (NP == 4) {
+      uint32_t h = ((uint32_t)myrow + a.seed) * 0x9E3779B1u;
+      h ^= h >> 15; h *= 0x85EBCA77u;
+      rowkey = h >> 24;
+    }
     if (lane < R && inb) { ob += lo.obj; gi += lo.resid; ui += lo.wgt; }
 #pragma unroll
     for (int r = 0; r < R; r++) {
@@ -353,14 +382,18 @@ k_oz_rows(const OzRowsArgs a) {
       const double ww = __shfl_sync(0xffffffffu, lo.wgt, r);
       const double sq = __shfl_sync(0xffffffffu, sw, r);
       uint32_t lo32[8], hi32[8];
+      uint32_t dlo = 0;
+      if constexpr (NP == 4) dlo = (__shfl_sync(0xffffffffu, rowkey, r) ^ lane_key) | DITHER_LO;
 #pragma unroll
       for (int e = 0; e < 8; e++) {
         g[e] = fma(rr, xv[r][e], g[e]);
         u[e] = fma(ww, xv[r][e], u[e]);
-        const double t = fma(xv[r][e], __dmul_rn(sq, cs[e]), MAGIC);
+        // four planes: element slot e of this lane flips its own bits of the dither byte (0x1d * e: eight distinct bytes)
+        const double add = NP == 5 ? MAGIC : __hiloint2double((int)0x43380080u, (int)(dlo ^ (uint32_t)(0x1d * e)));
+        const double t = fma(xv[r][e], __dmul_rn(sq, cs[e]), add);
         lo32[e] = (uint32_t)__double2loint(t);
         hi32[e] = (uint32_t)__double2hiint(t);
-        bad |= (hi32[e] ^ 0x43380000u) & 0xffffff00u;
+        bad |= (hi32[e] ^ HI_OK) & HI_MASK;
       }
       const int64_t row = row0 + r;
       if (row < n) {
@@ -371,23 +404,26 @@ k_oz_rows(const OzRowsArgs a) {
           // 4x4 byte transpose of the low words: w_s = {byte s of element 0, 1, 2, 3}
           const uint32_t t01a = prmt(L[0], L[1], 0x5140), t01b = prmt(L[0], L[1], 0x7362);
           const uint32_t t23a = prmt(L[2], L[3], 0x5140), t23b = prmt(L[2], L[3], 0x7362);
-          const uint32_t w0 = prmt(t01a, t23a, 0x5410), w1 = prmt(t01a, t23a, 0x7632);
+          const uint32_t w1 = prmt(t01a, t23a, 0x7632);
           const uint32_t w2 = prmt(t01b, t23b, 0x5410), w3 = prmt(t01b, t23b, 0x7632);
           const uint32_t w4 = prmt(prmt(H[0], H[1], 0x0040), prmt(H[2], H[3], 0x0040), 0x5410);
           const int off = r * OZ_COLS + h * OZ_HALF;
-          // plane p holds digit s = 4 - p; signed digit = byte ^ 0x80; columns beyond d stay zero (the planes are
+          // plane p holds digit s = 4 - p (byte 4 - p of the 40-bit value); signed digit = byte ^ 0x80; columns beyond d stay zero (the planes are
           // read 256 wide)
           const bool valid = h ? vB : vA;
           *reinterpret_cast<uint32_t*>(pl[0] + off) = valid ? (w4 ^ 0x80808080u) : 0u;
           *reinterpret_cast<uint32_t*>(pl[1] + off) = valid ? (w3 ^ 0x80808080u) : 0u;
           *reinterpret_cast<uint32_t*>(pl[2] + off) = valid ? (w2 ^ 0x80808080u) : 0u;
           *reinterpret_cast<uint32_t*>(pl[3] + off) = valid ? (w1 ^ 0x80808080u) : 0u;
-          *reinterpret_cast<uint32_t*>(pl[4] + off) = valid ? (w0 ^ 0x80808080u) : 0u;
+          if constexpr (NP == 5) {
+            const uint32_t w0 = prmt(t01a, t23a, 0x5410);
+            *reinterpret_cast<uint32_t*>(pl[4] + off) = valid ? (w0 ^ 0x80808080u) : 0u;
+          }
         }
       }
     }
 #pragma unroll
-    for (int p = 0; p < OZ_S; p++) pl[p] += pl_step;
+    for (int p = 0; p < NP; p++) pl[p] += pl_step;
   }
   if (bad) atomicExch(a.flag, 1);
 
@@ -450,7 +486,7 @@ __device__ __forceinline__ void oz_cluster_sync() {
 __device__ __forceinline__ uint64_t oz_desc(uint32_t saddr) {
   uint64_t dsc = 0;
   dsc |= (uint64_t)((saddr >> 4) & 0x3fff);
-  dsc |= (uint64_t)((OZ_TILE >> 4) & 0x3fff) << 16;      // leading byte offset (unused: one atom along MN)
+  dsc |= (uint64_t)1 << 16;                              // leading byte offset (unused: one atom along MN)
   dsc |= (uint64_t)((8 * OZ_HALF) >> 4) << 32;           // stride byte offset: next group of 8 rows
   dsc |= (uint64_t)1 << 46;                              // descriptor version
   dsc |= (uint64_t)2 << 61;                              // SWIZZLE_128B
@@ -461,7 +497,7 @@ constexpr uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | 
 
 struct OzGemmArgs {
   int64_t n;
-  int range_rows;           // rows per accumulation item (multiple of OZ_KC)
+  int range_rows;           // rows per accumulation item (multiple of OZ_KC_MAX)
   int nranges;
   int lanes;                // pairs per group
   int32_t* part;            // [nranges][OZ_GROUPS][OZ_SLOTS][256][256]
@@ -471,8 +507,11 @@ struct OzGemmArgs {
 
 // Pair p works for group p % 4 on the row ranges p / 4, p / 4 + lanes, ...: the four pairs of a lane walk the same rows;
 // whichever asks for a tile first brings it into L2 and the others mostly find it there.
+template <int KC>
 __global__ void __launch_bounds__(192, 1)
 k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
+  constexpr uint32_t OZ_TILE = KC * OZ_HALF;                   // one plane, one column half, one stage: 8 or 16 KB
+  constexpr int OZ_TILES = OZ_SMEM_TILES / (int)OZ_TILE;
   extern __shared__ __align__(1024) uint8_t oz_raw[];
   uint8_t* tiles = (uint8_t*)(((uintptr_t)oz_raw + 1023) & ~(uintptr_t)1023);       // [stage][plane slot][64][128]
   uint8_t* zero_tile = tiles + (size_t)(OZ_TILES - 1) * OZ_TILE;                      // the last tile stays zero
@@ -504,7 +543,7 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = tmem_base_s;
 
-  const int chunks_per_range = a.range_rows / OZ_KC;
+  const int chunks_per_range = a.range_rows / KC;
 
   if (warp == 0) {
     // ------------------------------------------------------------ producer (both CTAs): TMA tensor copies
@@ -515,7 +554,7 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
       for (int range = lane_id; range < a.nranges; range += a.lanes) {
         const int64_t r0 = (int64_t)range * a.range_rows;
         int64_t rem = a.n - r0;
-        const int nch = (int)((rem < a.range_rows ? (rem + OZ_KC - 1) / OZ_KC : chunks_per_range));
+        const int nch = (int)((rem < a.range_rows ? (rem + KC - 1) / KC : chunks_per_range));
         for (int ch = 0; ch < nch; ch++, it++) {
           oz_mbar_wait(&empty[st], ph);
           if (rank == 0) oz_mbar_expect_tx(&full[st], 2u * (uint32_t)np * OZ_TILE);
@@ -523,7 +562,7 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
           if (a.debug) dbg_issue[st] = clock64();
           const uint32_t bar = lead_full0 + (uint32_t)st * 8u;
           const int c0 = (int)rank * OZ_HALF;
-          const int c1 = (int)(r0 + (int64_t)ch * OZ_KC);
+          const int c1 = (int)(r0 + (int64_t)ch * KC);
           for (int q = 0; q < np; q++) {
             const uint32_t dst = oz_smem(tiles + ((size_t)st * np + q) * OZ_TILE);
             const int c2 = c_oz_planes[a.scheme][group][q];
@@ -575,7 +614,7 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
       for (int range = lane_id; range < a.nranges; range += a.lanes, item++) {
         const int64_t r0 = (int64_t)range * a.range_rows;
         int64_t rem = a.n - r0;
-        const int nch = (int)((rem < a.range_rows ? (rem + OZ_KC - 1) / OZ_KC : chunks_per_range));
+        const int nch = (int)((rem < a.range_rows ? (rem + KC - 1) / KC : chunks_per_range));
         if (item > 0) oz_mbar_wait(&acc_empty, (unsigned)((item - 1) & 1));      // the epilogue has drained the accumulators
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         for (int ch = 0; ch < nch; ch++) {
@@ -590,7 +629,7 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
             const uint32_t au = base_u + a_off[k];
             const uint32_t bu = b_fixed[k] ? b_off[k] : base_u + b_off[k];
 #pragma unroll
-            for (int ks = 0; ks < OZ_KC / 32; ks++) {
+            for (int ks = 0; ks < KC / 32; ks++) {
               const uint64_t ad = desc_hi | (uint64_t)((au + ks * KSTEP) & 0x3fffu);
               const uint64_t bd = desc_hi | (uint64_t)((bu + ks * KSTEP) & 0x3fffu);
               const uint32_t acc = (ch > 0 || ks > 0 || !first[k]) ? 1u : 0u;
@@ -677,7 +716,7 @@ struct OzFinishArgs {
   const OzPrep* prep;
   int ew;
   const int* flag;
-  int scheme;
+  int scheme, nplanes;
   double* out;              // d x d corner, row stride ldc
 };
 
@@ -703,11 +742,13 @@ k_oz_finish(const OzFinishArgs a) {
         if (c_oz_slot_off[a.scheme][g][s]) v += t[j * 256 + i];
         lev[level] += v;
       }
-    // sum_L lev[L] 256^(8-L), smallest terms first; every term is exact in double
+    // sum_L lev[L] 256^(2 (nplanes - 1) - L), smallest terms first; every term is exact in double
     double acc = 0.0;
+    const int top = 2 * (a.nplanes - 1);
 #pragma unroll
-    for (int L = OZ_LEVELS - 1; L >= 0; L--) acc += scalbn((double)lev[L], 8 * (8 - L));
-    const int qi = OZ_VBITS - a.prep->colexp[i] - a.ew, qj = OZ_VBITS - a.prep->colexp[j] - a.ew;
+    for (int L = OZ_LEVELS - 1; L >= 0; L--) acc += scalbn((double)lev[L], 8 * (top - L));
+    const int vb = oz_vbits(a.nplanes);
+    const int qi = vb - a.prep->colexp[i] - a.ew, qj = vb - a.prep->colexp[j] - a.ew;
     double h = (a.prep->colexp[i] == INT32_MIN || a.prep->colexp[j] == INT32_MIN) ? 0.0 : scalbn(scalbn(acc, -qi), -qj);
     if (poisoned) h = __longlong_as_double(0x7ff8000000000000ll);
     a.out[i * a.ldc + j] = h;
@@ -739,12 +780,12 @@ static OzPlan oz_plan(int device, int64_t n) {
   p.lanes = p.pairs / OZ_GROUPS;
   if (n < 1) n = 1;
   int64_t per_lane = (n + p.lanes - 1) / p.lanes;
-  int64_t rr = ((per_lane + OZ_KC - 1) / OZ_KC) * OZ_KC;
-  if (rr < OZ_KC) rr = OZ_KC;
+  int64_t rr = ((per_lane + OZ_KC_MAX - 1) / OZ_KC_MAX) * OZ_KC_MAX;
+  if (rr < OZ_KC_MAX) rr = OZ_KC_MAX;
   if (rr > OZ_MAX_RANGE) rr = OZ_MAX_RANGE;
   p.range_rows = (int)rr;
   int64_t chunk = OZ_CHUNK_ROWS;
-  if (const char* e = getenv("NUMS_B200_OZ_CHUNK_ROWS")) { const long long v = atoll(e); if (v >= OZ_KC) chunk = v; }   // tests
+  if (const char* e = getenv("NUMS_B200_OZ_CHUNK_ROWS")) { const long long v = atoll(e); if (v >= OZ_KC_MAX) chunk = v; }   // tests
   if ((n + chunk - 1) / chunk > OZ_MAX_CHUNKS) chunk = (n + OZ_MAX_CHUNKS - 1) / OZ_MAX_CHUNKS;
   chunk = ((chunk + rr - 1) / rr) * rr;
   if (chunk > n) chunk = ((n + rr - 1) / rr) * rr;
@@ -804,14 +845,17 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
   const int ew = family == NB_GLM_LINEAR ? 0 : -1;       // sqrt(w) <= 1 (linear), <= 1/2 (logistic: w = mu (1 - mu))
   *nparts = 0;
   if (phases & 1) NB_CHECK(cudaMemsetAsync(flag, 0, sizeof(int), st));
-  static KernelSetup rows_setup;
+  const int nplanes = h_oz_scheme_planes[scheme], kc = h_oz_scheme_kc[scheme];
+  static KernelSetup rows_setup5, rows_setup4;
   int occ = 1;
   const size_t rows_smem = (size_t)(OZ_ROWS_THREADS / 32) * OZ_ROWS_STAGES * OZ_R * OZ_COLS * sizeof(double);
-  if (int rc = rows_setup.get(device, k_oz_rows, OZ_ROWS_THREADS, rows_smem, &occ)) return rc;
-  const size_t smem = (size_t)OZ_TILES * OZ_TILE + 1024;
+  if (int rc = nplanes == 5 ? rows_setup5.get(device, k_oz_rows<5>, OZ_ROWS_THREADS, rows_smem, &occ)
+                            : rows_setup4.get(device, k_oz_rows<4>, OZ_ROWS_THREADS, rows_smem, &occ)) return rc;
+  const size_t smem = (size_t)OZ_SMEM_TILES + 1024;
   static bool gemm_ready[NB_MAX_DEVICES] = {};
   if (device < 0 || device >= NB_MAX_DEVICES || !gemm_ready[device]) {
-    NB_CHECK(cudaFuncSetAttribute(k_oz_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NB_CHECK(cudaFuncSetAttribute(k_oz_gemm<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NB_CHECK(cudaFuncSetAttribute(k_oz_gemm<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (device >= 0 && device < NB_MAX_DEVICES) gemm_ready[device] = true;
   }
   const int item = 8;                    // y is float64 or int64
@@ -831,7 +875,9 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
       if (grid > want) grid = want;
       if (grid < 1) grid = 1;
       ra.partials = parts + (size_t)(*nparts) * (2 * d + 3);
-      k_oz_rows<<<(unsigned)grid, OZ_ROWS_THREADS, rows_smem, st>>>(ra);
+      ra.seed = (uint32_t)(c0 / 64);
+      if (nplanes == 5) k_oz_rows<5><<<(unsigned)grid, OZ_ROWS_THREADS, rows_smem, st>>>(ra);
+      else k_oz_rows<4><<<(unsigned)grid, OZ_ROWS_THREADS, rows_smem, st>>>(ra);
       NB_LAUNCH_CHECK();
       *nparts += (int)grid;
     }
@@ -839,7 +885,7 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
       CUtensorMap tm;
       cuuint64_t dims[3] = {(cuuint64_t)OZ_COLS, (cuuint64_t)cn, (cuuint64_t)OZ_S};
       cuuint64_t strides[2] = {(cuuint64_t)OZ_COLS, (cuuint64_t)p.chunk_rows * OZ_COLS};
-      cuuint32_t box[3] = {OZ_HALF, OZ_KC, 1};
+      cuuint32_t box[3] = {OZ_HALF, (cuuint32_t)kc, 1};
       cuuint32_t estr[3] = {1, 1, 1};
       CUresult cr = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -858,7 +904,8 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
       at[0].id = cudaLaunchAttributeClusterDimension;
       at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = 1;
-      NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm, tm, ga));
+      if (kc == 64) NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm<64>, tm, ga));
+      else NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm<128>, tm, ga));
     }
     ranges_done += cranges;
   }
@@ -869,7 +916,7 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
   NB_LAUNCH_CHECK();
   OzFinishArgs fa;
   fa.d = d; fa.ldc = d + 1; fa.sums = sums; fa.prep = (const OzPrep*)prep; fa.ew = ew;
-  fa.flag = flag; fa.out = stats; fa.scheme = scheme;
+  fa.flag = flag; fa.out = stats; fa.scheme = scheme; fa.nplanes = nplanes;
   const int64_t blocks = (d * (d + 1) / 2 + 255) / 256;
   k_oz_finish<<<(unsigned)blocks, 256, 0, st>>>(fa);
   NB_LAUNCH_CHECK();

@@ -17,6 +17,7 @@ from .device import DeviceBlock
 
 NB_GLM_INT8_HESSIAN = 4
 NB_GLM_INT8_NO_LEVEL5 = 32
+NB_GLM_INT8_FOUR_PLANES = 64
 _HESSIAN_MODES = ("fp64", "int8", "int8!")
 
 
@@ -45,6 +46,14 @@ def int8_flags(found, rows):
     flags = NB_GLM_INT8_HESSIAN
     if rows > 0 and 5.0 * 2.0 ** (2 * found.range_log2 - 38.6) / math.sqrt(rows) <= 1e-11:
         flags |= NB_GLM_INT8_NO_LEVEL5
+    # four planes instead of five: x sqrt(w) keeps 31 bits, with a dithered rounding whose errors are zero-mean and
+    # independent over the rows whatever the data.  Largest error of the 65536 entries of H, relative to sqrt(H_ii H_jj):
+    # ~ 6 * 2^(r - 31) / sqrt(n) measured (tests/test_gpu_glm.py::test_hessian_int8_four_planes); taken as 8 * ..., it
+    # must stay below 2e-11, a fifth of the parity bar -- blocks of >= 2.2e6 rows for Gaussian columns (r = 3)
+    planes = os.environ.get("NUMS_B200_INT8_PLANES", "auto")          # "4" / "5" pin the choice (tests, measurements)
+    if planes == "4" or (planes != "5" and rows > 0 and
+                         8.0 * 2.0 ** (found.range_log2 - 31) / math.sqrt(rows) <= 2e-11):
+        flags |= NB_GLM_INT8_FOUR_PLANES
     return flags
 
 
@@ -179,8 +188,9 @@ def glm_newton_fit(family, beta, l2vec, tol, max_iter, hessian, *blocks):
                     flags.append(int8_flags(found, x.shape[0]))
         if flags:
             mode |= NB_GLM_INT8_HESSIAN
-            if all(f & NB_GLM_INT8_NO_LEVEL5 for f in flags):
-                mode |= NB_GLM_INT8_NO_LEVEL5
+            for bit in (NB_GLM_INT8_NO_LEVEL5, NB_GLM_INT8_FOUR_PLANES):
+                if all(f & bit for f in flags):
+                    mode |= bit
     import ctypes as C
     VP, I64 = C.c_void_p * nb, C.c_int64 * nb
     rows = [x.shape[0] for x in xs]

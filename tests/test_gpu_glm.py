@@ -271,6 +271,64 @@ def test_hessian_int8_row_chunks(app, monkeypatch):
     assert np.array_equal(H, H.T)
 
 
+@pytest.mark.parametrize("family", ["logistic", "linear"])
+@pytest.mark.parametrize("n,d,ldx", [(40_000, 256, None), (1_153, 256, None), (63, 256, None), (20_001, 132, None),
+                                     (70_007, 200, 204), (300_001, 256, None)])
+def test_hessian_int8_four_planes(app, monkeypatch, family, n, d, ldx):
+    """The four-plane variant (NB_GLM_INT8_FOUR_PLANES: 31-bit fixed point, eight products, 128-row pipeline stages) is
+    chosen by itself only for blocks of millions of rows, where its rounding error ~ 2^(r - 31) / sqrt(n) is far below
+    1e-10 (the 2.4e6-row case above runs it at the 1e-10 bar).  Pinned here on small blocks it must meet the error
+    model fused.int8_flags selects by: 8 * 2^(r - 31) / sqrt(n), r = 3 for Gaussian columns; everything else unchanged."""
+    monkeypatch.setenv("NUMS_B200_INT8_PLANES", "4")
+    ydtype = np.int64 if family == "logistic" else np.float64
+    (H, g, obj), (H0, g0, obj0) = raw_stats(n, d, family, ydtype, ldx, seed=13, hessian="int8!")
+    assert rel_err(g, g0) < STAT_TOL and rel_err(obj, obj0) < STAT_TOL
+    assert np.array_equal(H, H.T)
+    s = np.sqrt(np.diag(H0))
+    bound = 8.0 * 2.0 ** (3 - 31) / np.sqrt(n)
+    assert np.max(np.abs(H - H0)[:-1, :-1] / np.outer(s, s)[:-1, :-1]) < bound
+    assert rel_err(H[-1], H0[-1]) < STAT_TOL           # the intercept row comes from the FP64 column sums
+
+
+def test_hessian_int8_four_planes_repeated_rows(app, monkeypatch):
+    """Round-to-nearest errors of identical rows add up coherently; the four-plane pass dithers its rounding so that
+    the 1 / sqrt(n) cancellation holds for ANY data.  200000 rows that are 50 distinct rows repeated: the error must
+    follow the bound for n = 200000 (without the dither it sits at the bound for n = 50, 60x higher)."""
+    from nums_b200 import device as dv, fused
+    monkeypatch.setenv("NUMS_B200_INT8_PLANES", "4")
+    rng = np.random.default_rng(31)
+    n, d, distinct = 200_000, 256, 50
+    X = np.tile(rng.standard_normal((distinct, d)), (n // distinct, 1))
+    y = np.tile((rng.random(distinct) < 0.4).astype(np.int64), n // distinct)
+    beta = rng.standard_normal(d + 1) * 0.03
+    s = dv.to_numpy(fused.glm_stats(dv.from_numpy(X, 0), dv.from_numpy(y, 0), dv.from_numpy(beta, 0), "logistic", True,
+                                    hessian="int8!"))
+    p = d + 1
+    H = s[: p * p].reshape(p, p)[:d, :d]
+    mu = 1.0 / (1.0 + np.exp(-(X[:distinct] @ beta[:d] + beta[d])))
+    w = mu * (1.0 - mu)
+    H0 = (n // distinct) * ((X[:distinct].T * w) @ X[:distinct])
+    sc = np.sqrt(np.diag(H0))
+    assert np.max(np.abs(H - H0) / np.outer(sc, sc)) < 8.0 * 2.0 ** (3 - 31) / np.sqrt(n)
+
+
+def test_hessian_int8_four_planes_row_chunks_and_foreign_scale(app, monkeypatch):
+    from nums_b200 import device as dv, fused
+    monkeypatch.setenv("NUMS_B200_INT8_PLANES", "4")
+    monkeypatch.setenv("NUMS_B200_OZ_CHUNK_ROWS", "65536")
+    (H, g, obj), (H0, g0, obj0) = raw_stats(230_001, 256, "logistic", np.int64, seed=22, hessian="int8!")
+    assert rel_err(g, g0) < STAT_TOL and rel_err(obj, obj0) < STAT_TOL and rel_err(H, H0) < 1e-9
+    rng = np.random.default_rng(5)
+    n, d = 5000, 256
+    small = dv.from_numpy(rng.standard_normal((n, d)) * 1e-3, 0)
+    big = dv.from_numpy(rng.standard_normal((n, d)), 0)
+    big.prep = fused.glm_prepare(small)
+    y = dv.from_numpy((rng.random(n) < 0.5).astype(np.int64), 0)
+    st = dv.to_numpy(fused.glm_stats(big, y, dv.from_numpy(np.zeros(d + 1), 0), "logistic", True, hessian="int8"))
+    p = d + 1
+    assert np.all(np.isnan(st[: p * p].reshape(p, p)[:d, :d]))
+
+
 def test_hessian_int8_rejects_a_foreign_column_scale(app):
     """The digit split relies on the block's own column maxima.  Handing the kernel the scales of another block
     (values up to 1000x larger than prepared for) must not give a plausible Hessian: H comes back NaN."""

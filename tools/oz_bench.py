@@ -21,11 +21,13 @@ eta = Xs @ bs[:d] + bs[d]
 mu = 1 / (1 + np.exp(-eta)); w = mu * (1 - mu)
 Xl = Xs.astype(np.longdouble)
 H_ref = np.asarray((Xl * w[:, None].astype(np.longdouble)).T @ Xl, dtype=np.float64)
-for mode in ("int8", "fp64"):
+for mode in ("int8/5", "int8/4", "fp64"):
+    os.environ["NUMS_B200_INT8_PLANES"] = mode[5:] or "auto"
+    mode = mode[:4]
     s = dv.to_numpy(fused.glm_stats(dv.from_numpy(Xs, 0), dv.from_numpy(ys, 0), dv.from_numpy(bs, 0), "logistic", True,
                                     hessian=mode))
     H = s[: (d + 1) ** 2].reshape(d + 1, d + 1)[:d, :d]
-    print("accuracy %s: max|dH|/max|H| = %.3e" % (mode, np.max(np.abs(H - H_ref)) / np.max(np.abs(H_ref))), flush=True)
+    print("accuracy %s (planes %s): max|dH|/max|H| = %.3e" % (mode, os.environ["NUMS_B200_INT8_PLANES"], np.max(np.abs(H - H_ref)) / np.max(np.abs(H_ref))), flush=True)
 
 base = dv.from_numpy(rng.standard_normal(1 << 22), 0)
 X = dv.empty((n * d,), np.float64, 0)
@@ -56,9 +58,41 @@ def prep():
 
 
 print("prepare (column maxima, once per block): %.3f ms" % timed(prep), flush=True)
-for mode in ("int8", "fp64"):
+for mode in ("int8/5", "int8/4", "int8/auto", "fp64"):
+    os.environ["NUMS_B200_INT8_PLANES"] = mode[5:] or "auto"
+    planes, mode = mode[5:], mode[:4]
     ms = timed(lambda: fused.glm_stats(X, y, beta, "logistic", True, need_obj=False, hessian=mode))
-    print("stats pass %s: %.3f ms  %.0f GB/s algorithmic" % (mode, ms, n * (8 * d + 8) / ms / 1e6), flush=True)
-a = dv.to_numpy(fused.glm_stats(X, y, beta, "logistic", True, hessian="int8"))
+    print("stats pass %s %s: %.3f ms  %.0f GB/s algorithmic" % (mode, planes, ms, n * (8 * d + 8) / ms / 1e6), flush=True)
+from nums_b200 import _lib
+lib = _lib.load()
+stats_d = dv.empty((lib.nb_glm_stats_len(d),), np.float64, 0)
+prep_found = fused.glm_prepare(X)
+for planes in ("5", "4"):
+    os.environ["NUMS_B200_INT8_PLANES"] = planes
+    flags = 3 | fused.int8_flags(prep_found, n)
+    sc = dv.scratch(lib.nb_glm_scratch_bytes(0, n, d, flags), 0)
+    for name, extra in (("rows", 8), ("products", 16)):
+        ms = timed(lambda: _lib.check(lib.nb_glm_stats_prepared(0, 1, X.ptr, n, d, d, y.ptr, y.code, beta.ptr, flags | extra,
+                                                                prep_found.buf.data_ptr(), stats_d.ptr, sc.data_ptr(), sc.numel(),
+                                                                dv.stream_ptr(0))))
+        print("  %s planes, %s only: %.3f ms" % (planes, name, ms), flush=True)
+    del sc
+# per-kernel times inside a back-to-back loop of whole passes (CUPTI activity records: the kernels at the clocks of the loop)
+from torch.profiler import profile, ProfilerActivity
+for planes in ("5", "4"):
+    os.environ["NUMS_B200_INT8_PLANES"] = planes
+    run = lambda: fused.glm_stats(X, y, beta, "logistic", True, need_obj=False, hessian="int8")
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(10):
+            run()
+        torch.cuda.synchronize()
+    for ev in sorted(prof.key_averages(), key=lambda e: -e.device_time_total)[:4]:
+        print("  in-loop, %s planes: %-50s %8.3f ms x %d" % (planes, ev.key[:50], ev.device_time_total / ev.count / 1e3, ev.count), flush=True)
 b = dv.to_numpy(fused.glm_stats(X, y, beta, "logistic", True, hessian="fp64"))
-print("full size: max|int8 - fp64| / max|fp64| = %.3e" % (np.max(np.abs(a - b)) / np.max(np.abs(b))))
+for planes in ("5", "4"):
+    os.environ["NUMS_B200_INT8_PLANES"] = planes
+    a = dv.to_numpy(fused.glm_stats(X, y, beta, "logistic", True, hessian="int8"))
+    print("full size, %s planes: max|int8 - fp64| / max|fp64| = %.3e" % (planes, np.max(np.abs(a - b)) / np.max(np.abs(b))))
