@@ -395,6 +395,9 @@ int tri_gram(int device, const double* x, int64_t n, int64_t d, int64_t ldx, con
 // glm_ozaki.cu: X^T diag(w) X on the int8 tensor path (tcgen05), 128 < d <= 256
 bool oz_applicable(int family, int64_t n, int64_t d, int64_t ldx, const double* x);
 size_t oz_scratch_bytes(int device, int64_t n);
+bool oz_rows_applicable(int64_t n, int64_t d, int64_t ldx, const double* x);
+int oz_gradient_rows(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                     const double* beta, int skip_obj, double* parts, int max_parts, int* nparts, cudaStream_t st);
 int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
                  const double* beta, int skip_obj, const void* prep, double* stats, double* parts, int max_parts,
                  int* nparts, void* scratch, size_t scratch_bytes, int phases, int scheme, cudaStream_t st);
@@ -564,6 +567,15 @@ int nb_glm_stats_prepared(int device, int family, const double* x_d, int64_t n, 
       k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, np, parts, want_hess, stats_d);
       NB_LAUNCH_CHECK();
     }
+    return 0;
+  }
+  if (!want_hess && oz_rows_applicable(n, d, ldx, x_d)) {
+    // gradient / objective pass for 128 < d <= 256: the bulk-copy ring of the int8 path's row kernel (k_oz_rows<0>)
+    int np = 0;
+    int rc = oz_gradient_rows(device, family, x_d, n, d, ldx, y_d, ydt, beta_d, skip_obj, parts, L.max_parts, &np, st);
+    if (rc) return rc;
+    k_glm_rows_finish<<<(unsigned)((2 * d + 3 + 7) / 8), 256, 0, st>>>(d, np, parts, want_hess, stats_d);
+    NB_LAUNCH_CHECK();
     return 0;
   }
   const bool tri_ok = want_hess && fused_applicable(n, d, ldx, x_d);

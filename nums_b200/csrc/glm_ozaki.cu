@@ -263,6 +263,7 @@ k_oz_rows(const OzRowsArgs a) {
   for (int e = 0; e < 8; e++) {
     const int col = (e < 4 ? cA : cB) + (e & 3);
     bet[e] = col < d ? a.beta[col] : 0.0;
+    if constexpr (NP == 0) { cs[e] = 0.0; continue; }
     const int ce = a.prep->colexp[col];
     // v = x sqrt(w) 2^q with q = 38 - colexp - ew, so that |v| < 2^38 (four planes drop the lowest byte after a dither)
     int q = oz_vbits(5) - ce - a.ew;
@@ -304,7 +305,7 @@ k_oz_rows(const OzRowsArgs a) {
   if (first < nbatches && first * R + (lane % R) < n) ynext = reinterpret_cast<const long long*>(a.y)[first * R + (lane % R)];
   // this lane's byte position in every plane for the first row of the batch: advanced once per batch, so that the forty
   // plane stores of a batch need no address arithmetic beyond constant offsets
-  int8_t* pl[NP];
+  int8_t* pl[NP > 0 ? NP : 1];
 #pragma unroll
   for (int p = 0; p < NP; p++) pl[p] = a.planes + p * a.plane_stride + first * R * OZ_COLS + cA;
   const int64_t pl_step = per_it * R * OZ_COLS;
@@ -390,6 +391,7 @@ k_oz_rows(const OzRowsArgs a) {
 #pragma unroll
       for (int e = 0; e < 8; e++) {
         g[e] = fma(rr, xv[r][e], g[e]);
+        if constexpr (NP == 0) continue;          // gradient / objective pass: no u, no digits
         u[e] = fma(ww, xv[r][e], u[e]);
         // four planes: element slot e of this lane flips its own bits of the dither byte (0x1d * e: eight distinct bytes)
         const double add = NP == 5 ? MAGIC : __hiloint2double((int)0x43380080u, (int)(dlo ^ (uint32_t)(0x1d * e)));
@@ -399,7 +401,7 @@ k_oz_rows(const OzRowsArgs a) {
         bad |= (hi32[e] ^ HI_OK) & HI_MASK;
       }
       const int64_t row = row0 + r;
-      if (row < n) {
+      if (NP > 0 && row < n) {
 #pragma unroll
         for (int h = 0; h < 2; h++) {
           const uint32_t* L = lo32 + 4 * h;
@@ -1162,6 +1164,34 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
   const int64_t blocks = (d * (d + 1) / 2 + 255) / 256;
   k_oz_finish<<<(unsigned)blocks, 256, 0, st>>>(fa);
   NB_LAUNCH_CHECK();
+  return 0;
+}
+
+// The gradient / objective pass (no Hessian: an L-BFGS evaluation, a line-search trial) through the row kernel's bulk-copy
+// ring, without digit planes: k_oz_rows<0>.  Same partials as k_glm_rows (the caller runs k_glm_rows_finish).
+bool oz_rows_applicable(int64_t n, int64_t d, int64_t ldx, const double* x) {
+  return n > 0 && d > 128 && d <= 256 && (d % 4 == 0) && (ldx % 4 == 0) && ((((uintptr_t)x) & 31) == 0) &&
+         !NB_ENV_FLAG("NUMS_B200_NO_RING_GRADIENT");
+}
+
+int oz_gradient_rows(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,
+                     const double* beta, int skip_obj, double* parts, int max_parts, int* nparts, cudaStream_t st) {
+  static KernelSetup setup;
+  int occ = 1;
+  const size_t rows_smem = (size_t)(OZ_ROWS_THREADS / 32) * OZ_ROWS_STAGES * OZ_R * OZ_COLS * sizeof(double);
+  if (int rc = setup.get(device, k_oz_rows<0>, OZ_ROWS_THREADS, rows_smem, &occ)) return rc;
+  OzRowsArgs ra;
+  ra.x = x; ra.n = n; ra.d = d; ra.ldx = ldx; ra.y = y; ra.ydt = ydt; ra.beta = beta;
+  ra.family = family; ra.skip_obj = skip_obj; ra.ew = 0; ra.prep = nullptr; ra.planes = nullptr; ra.plane_stride = 0;
+  ra.flag = nullptr; ra.seed = 0; ra.partials = parts;
+  int64_t want = ((n + OZ_R - 1) / OZ_R + (OZ_ROWS_THREADS / 32) - 1) / (OZ_ROWS_THREADS / 32);
+  int64_t grid = (int64_t)dev_info(device).sms * occ;
+  if (grid > max_parts) grid = max_parts;
+  if (grid > want) grid = want;
+  if (grid < 1) grid = 1;
+  k_oz_rows<0><<<(unsigned)grid, OZ_ROWS_THREADS, rows_smem, st>>>(ra);
+  NB_LAUNCH_CHECK();
+  *nparts = (int)grid;
   return 0;
 }
 

@@ -412,6 +412,31 @@ def test_register_resident_gradient_pass_wide(app, family, d):
         assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
 
 
+@pytest.mark.parametrize("n,d", [(3, 256), (9_001, 196), (20_003, 200), (65_537, 256)])
+@pytest.mark.parametrize("family", ["logistic", "poisson", "linear"])
+def test_ring_gradient_pass(app, family, n, d):
+    """192 < d <= 256 (multiples of 4): the gradient/objective evaluation runs through the bulk-copy ring of the int8
+    path's row kernel without digit planes (k_oz_rows<0>, csrc/glm_ozaki.cu): contiguous and row-strided blocks, ragged row
+    counts, fewer rows than one batch; NUMS_B200_NO_RING_GRADIENT sends the same block through k_glm_rows -- both against
+    the oracle."""
+    from nums_b200 import device as dv, fused
+    ydtype = np.float64 if family == "linear" else np.int64
+    rng = np.random.default_rng(100 + d)
+    X = rng.standard_normal((n, d)) / np.sqrt(d)
+    beta = rng.standard_normal(d + 1) * 0.5
+    y = ((rng.random(n) < 0.4) if family == "logistic" else
+         (rng.poisson(1.5, n) if family == "poisson" else rng.standard_normal(n))).astype(ydtype)
+    model = oglm.BlockedGLM(family, [X], [y])
+    fwd = model.forward(beta)
+    g0, obj0 = model.gradient(beta, fwd), model.objective(beta, fwd)
+    wide = np.zeros((n, d + 4))
+    wide[:, :d] = X
+    p = d + 1
+    for Xd in (dv.from_numpy(X, 0), dv.DeviceBlock(dv.from_numpy(wide, 0).t[:, :d])):
+        s = dv.to_numpy(fused.glm_stats(Xd, dv.from_numpy(y, 0), dv.from_numpy(beta, 0), family, False))
+        assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
+
+
 @pytest.mark.parametrize("d", [5, 16, 64, 100, 256, 300])
 def test_newton_statistics_without_the_objective(app, d):
     """NB_GLM_HESS_NO_OBJECTIVE (what newton() asks for): identical g and H, objective slot 0."""
