@@ -251,6 +251,10 @@ k_oz_rows(const OzRowsArgs a) {
   const int64_t d = a.d, n = a.n;
   for (int j = tid; j < OZ_COLS; j += OZ_ROWS_THREADS) { s_g[j] = 0.0; s_u[j] = 0.0; }
   if (tid < 4) s_sc[tid] = 0.0;
+  // The inner loop reads whole 256-wide rows of its ring without guards: columns beyond d and rows beyond n take part in
+  // the arithmetic with zero factors (beta, the column scale, the row's residual and weight are 0 there), so what they
+  // read only has to be finite: the ring starts out as zeros and afterwards holds rows of X.
+  for (int j = tid; j < NW * NS * R * OZ_COLS; j += OZ_ROWS_THREADS) oz_ring[j] = 0.0;
   if (tid < NW * NS) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((unsigned)__cvta_generic_to_shared(&ring_full[tid / NS][tid % NS])));
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
@@ -302,7 +306,9 @@ k_oz_rows(const OzRowsArgs a) {
   int stage = 0;
   unsigned phase = 0;
   long long ynext = 0;                      // y (float64 or int64: 8 bytes either way) of this lane's row in the next batch
-  if (first < nbatches && first * R + (lane % R) < n) ynext = reinterpret_cast<const long long*>(a.y)[first * R + (lane % R)];
+  // after the transposed reduction below, the eight lanes with (lane >> 3) == r hold eta of row r of the batch
+  const int myr = lane >> 3;
+  if (first < nbatches && first * R + myr < n) ynext = reinterpret_cast<const long long*>(a.y)[first * R + myr];
   // this lane's byte position in every plane for the first row of the batch: advanced once per batch, so that the forty
   // plane stores of a batch need no address arithmetic beyond constant offsets
   int8_t* pl[NP > 0 ? NP : 1];
@@ -313,7 +319,7 @@ k_oz_rows(const OzRowsArgs a) {
     const int64_t row0 = batch * R;
     // y of the row this lane evaluates was asked for one batch ago (as raw bits: converting an int64 at once would make
     // the warp wait for the load right there -- a fifth of all stall samples in the first version); ask for the next one
-    const int64_t myrow = row0 + (lane % R);
+    const int64_t myrow = row0 + myr;
     const bool inb = myrow < n;
     const long long ybits = ynext;
     {
@@ -341,16 +347,11 @@ k_oz_rows(const OzRowsArgs a) {
     double xv[R][8];
 #pragma unroll
     for (int r = 0; r < R; r++) {
-      const int64_t row = row0 + r;
       const double* xr = st_rows + (size_t)r * d;
-      if (row < n && vA) {
-        const double2 p0 = *reinterpret_cast<const double2*>(xr + cA), p1 = *reinterpret_cast<const double2*>(xr + cA + 2);
-        xv[r][0] = p0.x; xv[r][1] = p0.y; xv[r][2] = p1.x; xv[r][3] = p1.y;
-      } else { xv[r][0] = xv[r][1] = xv[r][2] = xv[r][3] = 0.0; }
-      if (row < n && vB) {
-        const double2 p0 = *reinterpret_cast<const double2*>(xr + cB), p1 = *reinterpret_cast<const double2*>(xr + cB + 2);
-        xv[r][4] = p0.x; xv[r][5] = p0.y; xv[r][6] = p1.x; xv[r][7] = p1.y;
-      } else { xv[r][4] = xv[r][5] = xv[r][6] = xv[r][7] = 0.0; }
+      const double2 p0 = *reinterpret_cast<const double2*>(xr + cA), p1 = *reinterpret_cast<const double2*>(xr + cA + 2);
+      const double2 p2 = *reinterpret_cast<const double2*>(xr + cB), p3 = *reinterpret_cast<const double2*>(xr + cB + 2);
+      xv[r][0] = p0.x; xv[r][1] = p0.y; xv[r][2] = p1.x; xv[r][3] = p1.y;
+      xv[r][4] = p2.x; xv[r][5] = p2.y; xv[r][6] = p3.x; xv[r][7] = p3.y;
     }
     __syncwarp();                                  // every lane holds its part of the stage in registers: it may be refilled
     if (++stage == NS) { stage = 0; phase ^= 1u; }
@@ -360,15 +361,25 @@ k_oz_rows(const OzRowsArgs a) {
       double s0 = 0.0, s1 = 0.0;
 #pragma unroll
       for (int e = 0; e < 4; e++) { s0 = fma(xv[r][e], bet[e], s0); s1 = fma(xv[r][4 + e], bet[4 + e], s1); }
-      double s = s0 + s1;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      part[r] = s;
+      part[r] = s0 + s1;
     }
-    double eta = part[0];
-#pragma unroll
-    for (int r = 1; r < R; r++) if ((lane % R) == r) eta = part[r];
-    eta += beta0;
+    // four row sums over 32 lanes with 6 exchanges instead of 20: halves of the warp trade the rows they will not keep
+    double eta;
+    {
+      const bool up16 = (lane & 16) != 0, up8 = (lane & 8) != 0;
+      // lanes 0-15 keep rows 0,1 and lanes 16-31 rows 2,3
+      const double k0 = up16 ? part[2] : part[0], k1 = up16 ? part[3] : part[1];
+      const double g0 = up16 ? part[0] : part[2], g1 = up16 ? part[1] : part[3];
+      const double a0 = k0 + __shfl_xor_sync(0xffffffffu, g0, 16);
+      const double a1 = k1 + __shfl_xor_sync(0xffffffffu, g1, 16);
+      // bit 3 of the lane picks one of the two
+      const double keep = up8 ? a1 : a0, give = up8 ? a0 : a1;
+      double v = keep + __shfl_xor_sync(0xffffffffu, give, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 4);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      eta = v + beta0;
+    }
     const double yv = !inb ? 0.0 : (a.ydt == NB_F64 ? __longlong_as_double(ybits) : (double)ybits);
     LinkOut lo = a.skip_obj ? glm_link_noobj_rt(a.family, eta, yv) : glm_link_rt(a.family, eta, yv);
     if (!inb) { lo.resid = 0.0; lo.wgt = 0.0; lo.obj = 0.0; }
@@ -379,15 +390,15 @@ k_oz_rows(const OzRowsArgs a) {
       h ^= h >> 15; h *= 0x85EBCA77u;
       rowkey = h >> 24;
     }
-    if (lane < R && inb) { ob += lo.obj; gi += lo.resid; ui += lo.wgt; }
+    if ((lane & 7) == 0 && inb) { ob += lo.obj; gi += lo.resid; ui += lo.wgt; }
 #pragma unroll
     for (int r = 0; r < R; r++) {
-      const double rr = __shfl_sync(0xffffffffu, lo.resid, r);
-      const double ww = __shfl_sync(0xffffffffu, lo.wgt, r);
-      const double sq = __shfl_sync(0xffffffffu, sw, r);
+      const double rr = __shfl_sync(0xffffffffu, lo.resid, 8 * r);
+      const double ww = __shfl_sync(0xffffffffu, lo.wgt, 8 * r);
+      const double sq = __shfl_sync(0xffffffffu, sw, 8 * r);
       uint32_t lo32[8], hi32[8];
       uint32_t dlo = 0;
-      if constexpr (NP == 4) dlo = (__shfl_sync(0xffffffffu, rowkey, r) ^ lane_key) | DITHER_LO;
+      if constexpr (NP == 4) dlo = (__shfl_sync(0xffffffffu, rowkey, 8 * r) ^ lane_key) | DITHER_LO;
 #pragma unroll
       for (int e = 0; e < 8; e++) {
         g[e] = fma(rr, xv[r][e], g[e]);
@@ -398,7 +409,7 @@ k_oz_rows(const OzRowsArgs a) {
         const double t = fma(xv[r][e], __dmul_rn(sq, cs[e]), add);
         lo32[e] = (uint32_t)__double2loint(t);
         hi32[e] = (uint32_t)__double2hiint(t);
-        bad |= (hi32[e] ^ HI_OK) & HI_MASK;
+        bad |= hi32[e] ^ HI_OK;                     // (the digit byte of the high word is masked out at the end)
       }
       const int64_t row = row0 + r;
       if (NP > 0 && row < n) {
@@ -413,16 +424,15 @@ k_oz_rows(const OzRowsArgs a) {
           const uint32_t w2 = prmt(t01b, t23b, 0x5410), w3 = prmt(t01b, t23b, 0x7632);
           const uint32_t w4 = prmt(prmt(H[0], H[1], 0x0040), prmt(H[2], H[3], 0x0040), 0x5410);
           const int off = r * OZ_COLS + h * OZ_HALF;
-          // plane p holds digit s = 4 - p (byte 4 - p of the 40-bit value); signed digit = byte ^ 0x80; columns beyond d stay zero (the planes are
-          // read 256 wide)
-          const bool valid = h ? vB : vA;
-          *reinterpret_cast<uint32_t*>(pl[0] + off) = valid ? (w4 ^ 0x80808080u) : 0u;
-          *reinterpret_cast<uint32_t*>(pl[1] + off) = valid ? (w3 ^ 0x80808080u) : 0u;
-          *reinterpret_cast<uint32_t*>(pl[2] + off) = valid ? (w2 ^ 0x80808080u) : 0u;
-          *reinterpret_cast<uint32_t*>(pl[3] + off) = valid ? (w1 ^ 0x80808080u) : 0u;
+          // plane p holds digit s = 4 - p (byte 4 - p of the 40-bit value); signed digit = byte ^ 0x80; columns beyond d have
+          // scale 0, i.e. digits 0 (the planes are read 256 wide)
+          *reinterpret_cast<uint32_t*>(pl[0] + off) = w4 ^ 0x80808080u;
+          *reinterpret_cast<uint32_t*>(pl[1] + off) = w3 ^ 0x80808080u;
+          *reinterpret_cast<uint32_t*>(pl[2] + off) = w2 ^ 0x80808080u;
+          *reinterpret_cast<uint32_t*>(pl[3] + off) = w1 ^ 0x80808080u;
           if constexpr (NP == 5) {
             const uint32_t w0 = prmt(t01a, t23a, 0x5410);
-            *reinterpret_cast<uint32_t*>(pl[4] + off) = valid ? (w0 ^ 0x80808080u) : 0u;
+            *reinterpret_cast<uint32_t*>(pl[4] + off) = w0 ^ 0x80808080u;
           }
         }
       }
@@ -430,7 +440,7 @@ k_oz_rows(const OzRowsArgs a) {
 #pragma unroll
     for (int p = 0; p < NP; p++) pl[p] += pl_step;
   }
-  if (bad) atomicExch(a.flag, 1);
+  if (bad & HI_MASK) atomicExch(a.flag, 1);
 
   // CTA reduction in warp order (deterministic)
 #pragma unroll
