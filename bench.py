@@ -743,9 +743,11 @@ def run_ours(args, result):
         nprod = 8 if nplanes == 4 else (9 if (i8flags & fused.NB_GLM_INT8_NO_LEVEL5) else 11)
         int8_ops = nprod * 2.0 * 256 * 256 * n
         tensor = {
-            "bound": "tensor", "kernel": "k_oz_gemm (pass B: %d exact int8 plane products," % nprod + " tcgen05.mma kind::i8 cta_group::2, "
-                                         "TMA tensor copies, TMEM accumulators) + k_oz_reduce + k_oz_finish, timed alone "
-                                         "(NB_GLM_INT8_PRODUCTS_ONLY)",
+            "bound": "tensor", "kernel": "k_oz_gemm (pass B: %d exact int8 plane products," % nprod + " 72 CTA pairs, tcgen05.mma "
+                                         "kind::i8 cta_group::2, TMA tensor copies, TMEM accumulators) + k_oz_reduce + k_oz_finish, "
+                                         "timed alone (NB_GLM_INT8_PRODUCTS_ONLY), alternating with pass A as in a step",
+            "note": "ncu: the tensor pipe is busy 94-96 % of the kernel's active cycles (profiles/r02_ncu_oz_full.csv); the board "
+                    "runs this kernel at ~1.5 GHz of its 1.965 GHz, which is the distance to the nominal rate",
             "ms_per_launch": parts["products_ms"], "achieved": int8_ops / (parts["products_ms"] * 1e-3) / 1e12,
             "peak": INT8_TOPS_NOMINAL, "unit": "TOP/s", "frac": int8_ops / (parts["products_ms"] * 1e-3) / 1e12 / INT8_TOPS_NOMINAL,
             "peak_source": "nominal dense int8 (4.5 POP/s); MEASURED_PEAKS.json has no int8 figure",
@@ -786,7 +788,7 @@ def run_ours(args, result):
                                % (" | NB_GLM_INT8_HESSIAN" if int8_used else ""),
                        "ms_per_launch": parts.get("stats_int8_ms", parts["stats_fp64_ms"]),
                        "achieved": gram_bytes / (parts.get("stats_int8_ms", parts["stats_fp64_ms"]) * 1e-3) / 1e9, "unit": "GB/s"},
-        "gradient_pass": {"kernel": "k_glm_rows (eta/link/objective/gradient: the L-BFGS evaluation, HBM-bound)",
+        "gradient_pass": {"kernel": "k_oz_rows<0> (eta/link/objective/gradient through the bulk-copy ring: the L-BFGS evaluation at 192 < d <= 256, HBM-bound)",
                           "ms_per_launch": grad_ms, "achieved": gram_bytes / (grad_ms * 1e-3) / 1e9, "peak": hbm_peak,
                           "unit": "GB/s", "frac": gram_bytes / (grad_ms * 1e-3) / 1e9 / hbm_peak},
         "prepare_ms": prep_ms,

@@ -75,8 +75,8 @@ __constant__ OzProduct c_oz_products[OZ_SCHEMES][OZ_GROUPS][3] = {
      {{0, 2, 2}, {1, 1, 1}, {-1, 0, 0}},       // level 4, (2,2) | level 2, (1,1)
      {{0, 0, 2}, {-1, 0, 0}, {-1, 0, 0}}},     // level 2, (0,2) | (slot 1 unused)
     // scheme 2: FOUR planes (31-bit values), levels 0..4: eight products, two per group, every accumulator slot in use.
-    // Groups 0+1 read planes {0,1,3} between them and groups 2+3 planes {0,1,2}: k_oz_gemm_mc runs each such couple as
-    // one cluster that fetches its three planes once
+    // Three groups pair a p = p' product with a p < p' one on two planes; the fourth needs three planes: nine plane reads
+    // per stage for eight products
     {{{0, 0, 3}, {1, 1, 3}, {-1, 0, 0}},       // level 3, (0,3) | level 4, (1,3)
      {{0, 0, 1}, {1, 0, 0}, {-1, 0, 0}},       // level 1, (0,1) | level 0
      {{0, 0, 2}, {1, 2, 2}, {-1, 0, 0}},       // level 2, (0,2) | level 4, (2,2)
@@ -711,189 +711,6 @@ k_oz_gemm(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" :: "r"(tmem_base));
 }
 
-// ------------------------------------------------------------------------------------------------ pass B, four planes
-// The four-plane products with clusters of FOUR CTAs: two pairs that run two groups on the same rows, stage by stage.
-// Groups 0+1 need planes {0,1,3} between them, groups 2+3 planes {0,1,2}; a cluster fetches each of its three planes
-// ONCE per stage and the copy engine delivers the tile to every CTA that uses it (TMA multicast into the same stage slot
-// of each destination).  The planes are then read 6 times per pass (6 B per element of X) instead of the 9-11 B the
-// independent pairs of k_oz_gemm ask for, and the pass is bound by the tensor pipe.  (Clusters of eight - all four
-// groups, every plane read once - fit only 15 times on the 148 SMs: 60 pairs instead of 72, and the pass is MMA-bound.)
-//   full[s]  (pair leader)   one arrival + the bytes of the pair's tiles of stage s: armed by the MMA thread itself, for the
-//                            stage's next use, right after it has seen the current one complete
-//   empty[s] (every CTA)     one arrival per pair that reads what this CTA fetches: tcgen05.commit of that pair's MMAs
-// CTAs 0,1 of a cluster fetch its first two planes (each its own column half), CTAs 2,3 the third.
-// TMA multicast loads here read only this GPU's memory (the digit planes in the call's own scratch; oz_glm_stats checks
-// where that buffer lives and takes k_oz_gemm otherwise).
-constexpr int MC_KC = 128;                                   // rows per stage
-constexpr uint32_t MC_TILE = MC_KC * OZ_HALF;                // 16 KB: one plane, one column half, one stage
-constexpr int MC_STAGES = 4;
-constexpr int MC_SLOTS = 3;                                  // plane p sits in slot min(p, 2): no group reads planes 2 and 3
-constexpr uint32_t MC_STAGE = MC_SLOTS * MC_TILE;
-constexpr int MC_CLUSTER = 4;
-constexpr int MC_SCHEME = 2;
-__host__ __device__ constexpr uint32_t mc_planes_of(int g) { return g == 0 ? 0xBu : (g == 1 ? 0x3u : (g == 2 ? 0x5u : 0x6u)); }   // bit p: group g reads plane p
-__host__ __device__ constexpr int mc_cluster_plane(int type, int i) { return i < 2 ? i : (type == 0 ? 3 : 2); }    // the cluster's three planes
-__host__ __device__ constexpr uint32_t mc_slot(int p) { return p < 2 ? (uint32_t)p : 2u; }
-
-constexpr int MC_THREADS = 192;             // warp 0 fetch, warp 1 MMA issue, warps 2..5 epilogue
-__global__ void __launch_bounds__(MC_THREADS, 1)
-k_oz_gemm_mc(const __grid_constant__ CUtensorMap tmap, const OzGemmArgs a) {
-  extern __shared__ __align__(1024) uint8_t oz_raw[];
-  uint8_t* tiles = (uint8_t*)(((uintptr_t)oz_raw + 1023) & ~(uintptr_t)1023);       // [stage][slot][128][128]
-  __shared__ __align__(8) uint64_t full[MC_STAGES], empty[MC_STAGES], acc_full, acc_empty;
-  __shared__ uint32_t tmem_base_s;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t crank = oz_cluster_rank();
-  const uint32_t rank = crank & 1u, leader = crank & ~1u;
-  const int cid = (int)(blockIdx.x / MC_CLUSTER);
-  const int type = cid & 1, lane_id = cid >> 1;
-  const int group = 2 * type + (int)(crank >> 1);
-  const uint32_t my_planes = mc_planes_of(group);
-  const int np = __popc(my_planes);
-  // what this CTA fetches for the cluster (its own column half of these planes), who receives it, and who reads it
-  const int nfetch = (crank >> 1) == 0 ? 2 : 1;
-  int fetch_plane[2];
-  uint32_t fetch_mask[2] = {0, 0}, user_pairs = 0;
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    fetch_plane[i] = mc_cluster_plane(type, (crank >> 1) == 0 ? i : 2);
-    if (i < nfetch)
-      for (int j = 0; j < 2; j++)
-        if ((mc_planes_of(2 * type + j) >> fetch_plane[i]) & 1u) { fetch_mask[i] |= 1u << (2 * j + (int)rank); user_pairs |= 1u << j; }
-  }
-  const uint32_t users = (uint32_t)__popc(user_pairs);
-
-  // stages this lane will run (every CTA of the cluster counts the same)
-  const int chunks_per_range = a.range_rows / MC_KC;
-  int total = 0;
-  for (int range = lane_id; range < a.nranges; range += a.lanes) {
-    const int64_t rem = a.n - (int64_t)range * a.range_rows;
-    total += (int)(rem < a.range_rows ? (rem + MC_KC - 1) / MC_KC : chunks_per_range);
-  }
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < MC_STAGES; s++) { oz_mbar_init(&full[s], 1); oz_mbar_init(&empty[s], users); }
-    oz_mbar_init(&acc_full, 1);
-    oz_mbar_init(&acc_empty, 8);          // four epilogue warps (2..5) of each CTA of the pair
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    if (rank == 0)
-      for (int s = 0; s < MC_STAGES && s < total; s++) oz_mbar_expect_tx(&full[s], 2u * (uint32_t)np * MC_TILE);
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(oz_smem(&tmem_base_s)));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
-  }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  oz_cluster_sync();
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_base = tmem_base_s;
-
-  if (warp == 0) {
-    // ------------------------------------------------------------ fetch (every CTA): one multicast tensor copy per stage
-    if (lane == 0) {
-      const uint32_t lead_full0 = oz_smem(&full[0]) & 0xFEFFFFFFu;      // in each destination: its pair leader's barrier
-      const uint32_t dst0 = oz_smem(tiles);
-      const int c0 = (int)rank * OZ_HALF;
-      int st = 0;
-      unsigned ph = 1;                        // parity that lets the first pass over the ring through
-      for (int range = lane_id; range < a.nranges; range += a.lanes) {
-        const int64_t r0 = (int64_t)range * a.range_rows;
-        const int64_t rem = a.n - r0;
-        const int nch = (int)(rem < a.range_rows ? (rem + MC_KC - 1) / MC_KC : chunks_per_range);
-        for (int ch = 0; ch < nch; ch++) {
-          oz_mbar_wait(&empty[st], ph);       // every pair that reads these slots has finished the MMAs of their last use
-          const int c1 = (int)(r0 + (int64_t)ch * MC_KC);
-#pragma unroll
-          for (int i = 0; i < 2; i++) {
-            if (i < nfetch)
-              asm volatile("cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-                           " [%0], [%1, {%3, %4, %5}], [%2], %6;"
-                           :: "r"(dst0 + (uint32_t)st * MC_STAGE + mc_slot(fetch_plane[i]) * MC_TILE), "l"(&tmap),
-                              "r"(lead_full0 + (uint32_t)st * 8u), "r"(c0), "r"(c1), "r"(fetch_plane[i]),
-                              "h"((uint16_t)fetch_mask[i]) : "memory");
-          }
-          if (++st == MC_STAGES) { st = 0; ph ^= 1u; }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer (leader CTA of the pair, one thread)
-    // (a second issuing thread, one per product, changed nothing: the pass is bound by the bytes delivered into the SMs)
-    if (rank == 0 && lane == 0) {
-      uint32_t a_off[2], b_off[2], dcol[2];
-#pragma unroll
-      for (int k = 0; k < 2; k++) {
-        const OzProduct pr = c_oz_products[MC_SCHEME][group][k];
-        a_off[k] = mc_slot(pr.pa) * (MC_TILE >> 4);
-        b_off[k] = mc_slot(pr.pb) * (MC_TILE >> 4);
-        dcol[k] = tmem_base + (uint32_t)pr.slot * 256u;
-      }
-      // a stage's empty barrier lives in the CTAs that fetch this pair's planes
-      uint16_t commit_mask = 0;
-#pragma unroll
-      for (int i = 0; i < 3; i++) if ((my_planes >> mc_cluster_plane(type, i)) & 1u) commit_mask |= (uint16_t)(3u << (i < 2 ? 0 : 2));
-      const uint16_t pair_mask = (uint16_t)(3u << leader);
-      const uint64_t desc_hi = oz_desc(0);
-      const uint32_t tiles_u = oz_smem(tiles) >> 4;
-      constexpr uint32_t KSTEP = (32 * OZ_HALF) >> 4;
-      int item = 0, st = 0, it = 0;
-      unsigned ph = 0;
-      for (int range = lane_id; range < a.nranges; range += a.lanes, item++) {
-        const int64_t rem = a.n - (int64_t)range * a.range_rows;
-        const int nch = (int)(rem < a.range_rows ? (rem + MC_KC - 1) / MC_KC : chunks_per_range);
-        if (item > 0) oz_mbar_wait(&acc_empty, (unsigned)((item - 1) & 1));      // the epilogue has drained the accumulators
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        for (int ch = 0; ch < nch; ch++, it++) {
-          oz_mbar_wait(&full[st], ph);
-          // arm the barrier for the stage's next use: no byte of it can arrive before the commit below is seen
-          if (it + MC_STAGES < total) oz_mbar_expect_tx(&full[st], 2u * (uint32_t)np * MC_TILE);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t base_u = tiles_u + (uint32_t)st * (MC_STAGE >> 4);
-#pragma unroll
-          for (int k = 0; k < 2; k++) {
-#pragma unroll
-            for (int ks = 0; ks < MC_KC / 32; ks++) {
-              const uint64_t ad = desc_hi | (uint64_t)((base_u + a_off[k] + ks * KSTEP) & 0x3fffu);
-              const uint64_t bd = desc_hi | (uint64_t)((base_u + b_off[k] + ks * KSTEP) & 0x3fffu);
-              const uint32_t acc = (ch > 0 || ks > 0) ? 1u : 0u;
-              asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                           "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}"
-                           :: "r"(dcol[k]), "l"(ad), "l"(bd), "r"(OZ_IDESC), "r"(acc), "r"(0u) : "memory");
-            }
-          }
-          asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                       :: "r"(oz_smem(&empty[st])), "h"(commit_mask) : "memory");
-          if (++st == MC_STAGES) { st = 0; ph ^= 1u; }
-        }
-        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                     :: "r"(oz_smem(&acc_full)), "h"(pair_mask) : "memory");
-      }
-    }
-  } else {
-    // ------------------------------------------------------------ epilogue warps 2..5 (both CTAs of the pair)
-    const int q = warp & 3;                          // lane quarter of tensor memory this warp may read
-    int item = 0;
-    for (int range = lane_id; range < a.nranges; range += a.lanes, item++) {
-      oz_mbar_wait(&acc_full, (unsigned)(item & 1));
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const int row = (int)rank * 128 + q * 32 + lane;
-      for (int s = 0; s < OZ_SLOTS; s++) {
-        int32_t* dst = a.part + ((((size_t)range * OZ_GROUPS + group) * OZ_SLOTS + s) * 256 + row) * 256;
-        oz_drain_row(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * 256), dst);
-      }
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncwarp();
-      if (lane == 0) {
-        if (rank == 0) oz_mbar_arrive(&acc_empty);
-        else oz_mbar_arrive_remote(&acc_empty, leader);
-      }
-    }
-  }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  oz_cluster_sync();
-  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" :: "r"(tmem_base));
-}
-
 // ------------------------------------------------------------------------------------------------ finish
 // step 1: exact sums over the ranges, one thread per accumulator entry (coalesced)
 __global__ void __launch_bounds__(256)
@@ -970,34 +787,10 @@ constexpr int64_t OZ_CHUNK_ROWS = 12517376;            // 382 ranges of 32768 ro
 
 struct OzPlan {
   int range_rows, lanes, pairs;
-  bool multicast;                       // k_oz_gemm_mc (clusters of four CTAs) runs the products
   int nchunks; int64_t chunk_rows;      // rows per chunk (the last one may be shorter); a multiple of range_rows
   int nranges;                          // over all chunks
   size_t off_planes, off_part, off_sums, off_flag, total;
 };
-
-constexpr size_t OZ_MC_SMEM = (size_t)MC_STAGES * MC_STAGE + 1024;       // + alignment slack
-
-// clusters of four CTAs (k_oz_gemm_mc) the device runs at once; 0 if it takes none
-static int oz_mc_clusters(int device) {
-  static int cached[NB_MAX_DEVICES];
-  static bool known[NB_MAX_DEVICES] = {};
-  if (device >= 0 && device < NB_MAX_DEVICES && known[device]) return cached[device];
-  int clusters = 0;
-  if (cudaFuncSetAttribute(k_oz_gemm_mc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OZ_MC_SMEM) == cudaSuccess) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(MC_CLUSTER * 64); cfg.blockDim = dim3(MC_THREADS); cfg.dynamicSmemBytes = OZ_MC_SMEM;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = MC_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
-    if (cudaOccupancyMaxActiveClusters(&clusters, k_oz_gemm_mc, &cfg) != cudaSuccess) clusters = 0;
-  }
-  (void)cudaGetLastError();
-  if (NB_ENV_FLAG("NUMS_B200_OZ_NO_MULTICAST")) clusters = 0;
-  if (device >= 0 && device < NB_MAX_DEVICES) { cached[device] = clusters; known[device] = true; }
-  return clusters;
-}
 
 static OzPlan oz_plan(int device, int64_t n, int scheme) {
   OzPlan p;
@@ -1005,11 +798,6 @@ static OzPlan oz_plan(int device, int64_t n, int scheme) {
   p.pairs = ((sms / 2) / OZ_GROUPS) * OZ_GROUPS;
   if (p.pairs < OZ_GROUPS) p.pairs = OZ_GROUPS;
   p.lanes = p.pairs / OZ_GROUPS;
-  p.multicast = false;
-  if (scheme == 2) {
-    const int clusters = oz_mc_clusters(device);
-    if (clusters >= 2) { p.lanes = clusters / 2; p.pairs = p.lanes * OZ_GROUPS; p.multicast = true; }      // two clusters per lane
-  }
   if (n < 1) n = 1;
   // as few rounds of ranges per lane as the int32 accumulators allow, and ranges of equal length over those rounds
   const int64_t max_range = scheme == 2 ? OZ_MAX_RANGE_SINGLE : OZ_MAX_RANGE;
@@ -1045,17 +833,6 @@ bool oz_applicable(int family, int64_t n, int64_t d, int64_t ldx, const double* 
 size_t oz_scratch_bytes(int device, int64_t n) {
   const size_t a = oz_plan(device, n, 0).total, b = oz_plan(device, n, 2).total;
   return a > b ? a : b;
-}
-
-// true when [ptr, ptr + bytes) is ordinary device memory of `device` (not a peer's, not host or managed memory)
-static bool oz_local_memory(int device, const void* ptr, size_t bytes) {
-  const char* ends[2] = {(const char*)ptr, (const char*)ptr + (bytes ? bytes - 1 : 0)};
-  for (const char* q : ends) {
-    cudaPointerAttributes at;
-    if (cudaPointerGetAttributes(&at, q) != cudaSuccess) { (void)cudaGetLastError(); return false; }
-    if (at.type != cudaMemoryTypeDevice || at.device != device) return false;
-  }
-  return true;
 }
 
 typedef CUresult (*OzEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -1143,22 +920,18 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
       OzGemmArgs ga;
       ga.n = cn; ga.range_rows = p.range_rows; ga.nranges = cranges; ga.lanes = p.lanes; ga.scheme = scheme;
       ga.debug = NB_ENV_FLAG("NUMS_B200_OZ_DEBUG") ? 1 : 0;
-      if (ga.debug) fprintf(stderr, "int8 Hessian: scheme %d, %d lanes, ranges of %d rows, %d ranges, multicast plan %d\n", scheme, p.lanes,
-                            p.range_rows, cranges, (int)p.multicast);
+      if (ga.debug) fprintf(stderr, "int8 Hessian: scheme %d, %d lanes, ranges of %d rows, %d ranges\n", scheme, p.lanes, p.range_rows, cranges);
       ga.part = part + (size_t)ranges_done * OZ_GROUPS * OZ_SLOTS * 65536;
-      // the multicast kernel only when the planes are this device's own memory
-      const bool mc = p.multicast && oz_local_memory(device, planes, (size_t)OZ_S * (size_t)p.chunk_rows * OZ_COLS);
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3((unsigned)(2 * p.pairs));
-      cfg.blockDim = dim3(mc ? MC_THREADS : 192);
-      cfg.dynamicSmemBytes = mc ? OZ_MC_SMEM : smem;
+      cfg.blockDim = dim3(192);
+      cfg.dynamicSmemBytes = smem;
       cfg.stream = st;
       cudaLaunchAttribute at[1];
       at[0].id = cudaLaunchAttributeClusterDimension;
-      at[0].val.clusterDim.x = mc ? MC_CLUSTER : 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = 1;
-      if (mc) NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm_mc, tm, ga));
-      else if (kc == 64) NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm<64>, tm, ga));
+      if (kc == 64) NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm<64>, tm, ga));
       else NB_CHECK(cudaLaunchKernelEx(&cfg, k_oz_gemm<128>, tm, ga));
     }
     ranges_done += cranges;
