@@ -15,10 +15,14 @@
 // dropped levels are below 2^-48 of the column scale squared.  Rounding to v is the approximation that matters:
 // half a unit in 2^-38 of the column maximum per element.
 //
-//   pass A  k_oz_rows    reads X once (HBM-bound): eta, link, g, u, sum w as k_glm_rows does, and writes the five digit
-//                        planes [plane][row][256] (5 bytes per element instead of the 8 of w or of X*sqrt(w)).
+// Blocks of millions of rows (NB_GLM_INT8_FOUR_PLANES, scheme 2 below): the rounding errors of the rows cancel as 1 / sqrt(n), so
+// 31 bits per element are enough for the 1e-10 bar: FOUR planes, eight products (levels p + p' <= 4), one per accumulator.
+// The rounding to 31 bits is dithered (see k_oz_rows) so that the cancellation holds for any data, repeated rows included.
+//
+//   pass A  k_oz_rows    reads X once (HBM-bound): eta, link, g, u, sum w as k_glm_rows does, and writes the digit
+//                        planes [plane][row][256] (4 or 5 bytes per element instead of the 8 of w or of X*sqrt(w)).
 //   pass B  k_oz_gemm    CTA pairs (cta_group::2, M = 256, N = 256): TMA tensor copies (128-byte swizzle) bring
-//                        [64 rows][128 bytes] tiles of the planes a pair needs, one elected thread issues
+//                        [64 or 128 rows][128 bytes] tiles of the planes a pair needs, one elected thread issues
 //                        tcgen05.mma kind::i8 on MN-major operands, the accumulators of two "slots" fill the 512
 //                        tensor-memory columns.  Eight slots are needed (a slot holds same-level products of one
 //                        kind: P_pp' with p < p' enter H as P + P^T, P_pp once), so four groups of pairs work on the
@@ -55,11 +59,11 @@ __host__ __device__ constexpr int oz_vbits(int nplanes) { return nplanes == 5 ? 
 // products of each group: {slot, plane of A, plane of B}; planes the group stages.  Levels 0..5 (11 products, 8 slots:
 // the first dropped terms, level 6, are 2^-48 of the column scale squared).
 struct OzProduct { int slot, pa, pb; };
-// Two schemes.  0: levels 0..5, 11 products (any n).  1: levels 0..4, 9 products: the level-5 terms (1,4), (2,3) are sums of
+// Three schemes.  2: four planes, see the table.  0: levels 0..5, 11 products (any n).  1: levels 0..4, 9 products: the level-5 terms (1,4), (2,3) are sums of
 // n products of independent, zero-mean low digits, i.e. a relative contribution ~ 2^(2r - 38.6) / sqrt(n) to H (r = range_log2
 // of nb_glm_prepare); the caller drops them (NB_GLM_INT8_NO_LEVEL5) when that is below 1e-11 — at 1.25e7 Gaussian rows it is
-// 3e-13 — which removes four of the sixteen plane streams, and this kernel is bound by the L2 -> SM operand stream (measured:
-// time = streamed bytes / 6.6 TB/s in every variant tried).
+// 3e-13 — which removes four of the sixteen plane streams (ncu on scheme 2: the tensor pipe is busy 92 % of the elapsed cycles, the
+// kernel follows the clock the board grants it).
 // Grouping rule of scheme 0: no group stages more than four planes; every group stages four planes and issues three products per
 // stage, so the four pairs of a lane advance at the same pace and stay close: the pair that asks for a tile first pays the
 // trip to HBM, the others find it in L2.  Group 3 has only two useful products on three planes; its third is plane 3 against a
