@@ -293,7 +293,7 @@ k_oz_rows(const OzRowsArgs a) {
   uint32_t bad = 0;
   // Four planes keep 31 bits of x sqrt(w), and the 1e-10 bar on H then rests on the rounding errors of the n rows
   // cancelling (~ 1 / sqrt(n)).  Round-to-nearest errors do not cancel over REPEATED rows (one-hot data, tiled test
-  // matrices): the same row rounds the same way every time.  The dither byte is hash(row) ^ (a constant per column): a
+  // matrices): the same row rounds the same way every time.  The dither byte is hash(row) ^ (a constant per lane): a
   // given column sees independent uniform dithers down the rows, so its rounding errors are zero-mean and independent
   // of the data.  It depends on the row's position only: the same block gives the same bits.
   const uint32_t lane_key = ((uint32_t)lane * 0x9E3779B1u) >> 24;
@@ -403,20 +403,23 @@ k_oz_rows(const OzRowsArgs a) {
       uint32_t lo32[8], hi32[8];
       uint32_t dlo = 0;
       if constexpr (NP == 4) dlo = (__shfl_sync(0xffffffffu, rowkey, 8 * r) ^ lane_key) | DITHER_LO;
+      // four planes: one dither byte per (row, lane) serves the lane's eight columns -- what matters is that a COLUMN sees
+      // independent uniform bytes down the rows; columns sharing a byte only correlate their errors with each other, which
+      // enters H at second order (2^-57)
+      const double add = NP == 5 ? MAGIC : __hiloint2double((int)0x43380080u, (int)dlo);
 #pragma unroll
       for (int e = 0; e < 8; e++) {
         g[e] = fma(rr, xv[r][e], g[e]);
         if constexpr (NP == 0) continue;          // gradient / objective pass: no u, no digits
         u[e] = fma(ww, xv[r][e], u[e]);
-        // four planes: element slot e of this lane flips its own bits of the dither byte (0x1d * e: eight distinct bytes)
-        const double add = NP == 5 ? MAGIC : __hiloint2double((int)0x43380080u, (int)(dlo ^ (uint32_t)(0x1d * e)));
         const double t = fma(xv[r][e], __dmul_rn(sq, cs[e]), add);
         lo32[e] = (uint32_t)__double2loint(t);
         hi32[e] = (uint32_t)__double2hiint(t);
         bad |= hi32[e] ^ HI_OK;                     // (the digit byte of the high word is masked out at the end)
       }
-      const int64_t row = row0 + r;
-      if (NP > 0 && row < n) {
+      // (rows beyond n, at most three in the last batch, store zero digits: the plane buffer is a whole number of 128-row
+      // stages long, and pass B's tensor map ends at row n anyway)
+      if constexpr (NP > 0) {
 #pragma unroll
         for (int h = 0; h < 2; h++) {
           const uint32_t* L = lo32 + 4 * h;
