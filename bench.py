@@ -386,6 +386,8 @@ def run_lbfgs1024(args, result):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        # one process per GPU: keep this rank's host threads and the pages it touches first next to its GPU
+        dv.bind_host_to_gpu(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     app = set_instance(make_app(device_ids=[local]))
     km = app.km
@@ -473,7 +475,10 @@ def run_ours(args, result):
         if world == 1 and args.gpus > 1:
             raise SystemExit("--gpus %d needs torchrun (one process per GPU)" % args.gpus)
     torch.cuda.set_device(local)
+    bound_cpus = None
     if world > 1:
+        # one process per GPU: keep this rank's host threads and the pages it touches first next to its GPU
+        bound_cpus = dv.bind_host_to_gpu(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     app = set_instance(make_app(device_ids=[local]))
     km = app.km
@@ -692,6 +697,7 @@ def run_ours(args, result):
                "rows_per_gpu": e_rows, "seconds": dt, "upload_seconds": upload_s,
                "h2d_gbs_per_gpu": e_rows * d * 8 / upload_s / 1e9, "h2d_gbs_aggregate": world * e_rows * d * 8 / upload_s / 1e9,
                "compute_seconds_expected": K * ms_step * 1e-3,
+               "host_cpus_bound_rank0": len(bound_cpus) if bound_cpus else None,
                "what": "LogisticRegression.fit(host X, host y): upload from pinned host memory + %d Newton "
                        "iterations + coefficient read-back, per rank" % K}
         del Xh, yh

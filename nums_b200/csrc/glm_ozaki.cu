@@ -960,8 +960,7 @@ int oz_glm_stats(int device, int family, const double* x, int64_t n, int64_t d, 
 // The gradient / objective pass (no Hessian: an L-BFGS evaluation, a line-search trial) through the row kernel's bulk-copy
 // ring, without digit planes: k_oz_rows<0>.  Same partials as k_glm_rows (the caller runs k_glm_rows_finish).
 bool oz_rows_applicable(int64_t n, int64_t d, int64_t ldx, const double* x) {
-  return n > 0 && d > 128 && d <= 256 && (d % 4 == 0) && (ldx % 4 == 0) && ((((uintptr_t)x) & 31) == 0) &&
-         !NB_ENV_FLAG("NUMS_B200_NO_RING_GRADIENT");
+  return n > 0 && d > 128 && d <= 256 && (d % 4 == 0) && (ldx % 4 == 0) && ((((uintptr_t)x) & 31) == 0);
 }
 
 int oz_gradient_rows(int device, int family, const double* x, int64_t n, int64_t d, int64_t ldx, const void* y, int ydt,

@@ -97,6 +97,30 @@ class DeviceBlock:
         return "DeviceBlock(shape=%s, dtype=%s, cuda:%s)" % (self.shape, self.dtype, self.device_index)
 
 
+def bind_host_to_gpu(device_index):
+    """Restricts the calling process to the CPUs next to GPU `device_index` (NVML's ideal CPU set, i.e. the NUMA node of the
+    GPU's PCIe root), so that host buffers it allocates and first touches afterwards are local to that GPU.  For the
+    one-process-per-GPU layout on multi-socket hosts.  (The 8-GPU box of the round-2 measurements presents one NUMA node
+    of 32 CPUs for all GPUs: the call changes nothing there, and its 186 GB/s of aggregate upload are the host's limit.)
+    Returns the CPU list, or None when NVML or the topology is not available (nothing is changed then)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(device_index)
+        bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cpus = [64 * w + b for w, mask in enumerate(words) for b in range(64) if (int(mask) >> b) & 1]
+        allowed = sorted(set(cpus) & os.sched_getaffinity(0))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None
+
+
 def stream_ptr(device_index):
     return C.c_void_p(torch.cuda.current_stream(device_index).cuda_stream)
 

@@ -412,13 +412,13 @@ def test_register_resident_gradient_pass_wide(app, family, d):
         assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
 
 
-@pytest.mark.parametrize("n,d", [(3, 256), (9_001, 196), (20_003, 200), (65_537, 256)])
+@pytest.mark.parametrize("n,d", [(3, 256), (9_001, 196), (20_003, 200), (65_537, 256), (9_001, 254)])
 @pytest.mark.parametrize("family", ["logistic", "poisson", "linear"])
 def test_ring_gradient_pass(app, family, n, d):
     """192 < d <= 256 (multiples of 4): the gradient/objective evaluation runs through the bulk-copy ring of the int8
     path's row kernel without digit planes (k_oz_rows<0>, csrc/glm_ozaki.cu): contiguous and row-strided blocks, ragged row
-    counts, fewer rows than one batch; NUMS_B200_NO_RING_GRADIENT sends the same block through k_glm_rows -- both against
-    the oracle."""
+    counts, fewer rows than one batch.  A width or a row stride that is not a multiple of 4 (d = 254; the d + 3 window)
+    sends the block through k_glm_rows instead -- both against the oracle."""
     from nums_b200 import device as dv, fused
     ydtype = np.float64 if family == "linear" else np.int64
     rng = np.random.default_rng(100 + d)
@@ -429,10 +429,13 @@ def test_ring_gradient_pass(app, family, n, d):
     model = oglm.BlockedGLM(family, [X], [y])
     fwd = model.forward(beta)
     g0, obj0 = model.gradient(beta, fwd), model.objective(beta, fwd)
-    wide = np.zeros((n, d + 4))
-    wide[:, :d] = X
     p = d + 1
-    for Xd in (dv.from_numpy(X, 0), dv.DeviceBlock(dv.from_numpy(wide, 0).t[:, :d])):
+    blocks = [dv.from_numpy(X, 0)]
+    for pad in (4, 3):
+        wide = np.zeros((n, d + pad))
+        wide[:, :d] = X
+        blocks.append(dv.DeviceBlock(dv.from_numpy(wide, 0).t[:, :d]))
+    for Xd in blocks:
         s = dv.to_numpy(fused.glm_stats(Xd, dv.from_numpy(y, 0), dv.from_numpy(beta, 0), family, False))
         assert rel_err(s[p * p: p * p + p], g0) < STAT_TOL and rel_err(s[p * p + p], obj0) < STAT_TOL
 

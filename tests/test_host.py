@@ -243,3 +243,17 @@ def test_oracle_ref_is_an_unmodified_copy_of_the_reference():
         here = hashlib.sha256(open(os.path.join(make_ref.OUT, rel), "rb").read()).hexdigest()
         there = hashlib.sha256(open(os.path.join(REF, rel), "rb").read()).hexdigest()
         assert here == there == digest, rel
+
+
+def test_bind_host_to_gpu_changes_nothing_without_a_gpu():
+    """device.bind_host_to_gpu (NUMA placement of a rank's host buffers) must be harmless where NVML / CUDA are absent."""
+    import os
+    import torch
+    from nums_b200 import device as dv
+    before = os.sched_getaffinity(0)
+    got = dv.bind_host_to_gpu(0)
+    if not torch.cuda.is_available():
+        assert got is None and os.sched_getaffinity(0) == before
+    else:
+        assert got is None or set(got) <= before
+        os.sched_setaffinity(0, before)
