@@ -265,7 +265,6 @@ k_oz_rows(const OzRowsArgs a) {
 
   // this lane owns columns cA..cA+3 and cB..cB+3 (element slots 0..3 and 4..7)
   const int cA = 4 * lane, cB = OZ_HALF + 4 * lane;
-  const bool vA = cA < d, vB = cB < d;             // d is a multiple of 4
   double bet[8], cs[8];
 #pragma unroll
   for (int e = 0; e < 8; e++) {
