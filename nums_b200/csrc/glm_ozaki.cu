@@ -52,6 +52,10 @@ constexpr int OZ_MAX_RANGE_SINGLE = 65536;      // scheme 2: one product per acc
 constexpr int OZ_GROUPS = 4;
 constexpr int OZ_SLOTS = 2;
 constexpr int OZ_ROWS_THREADS = 256;
+// the gradient-only instantiation needs 168 registers: nine warps fit a scheduler's 16 K registers (three warps on one of the four),
+// and their 216 KB of ring the shared memory; the plane kernels (215 registers) spill at nine
+constexpr int OZ_GRAD_THREADS = 288;
+__host__ __device__ constexpr int oz_rows_threads(int nplanes) { return nplanes == 0 ? OZ_GRAD_THREADS : OZ_ROWS_THREADS; }
 constexpr int OZ_R = 4;                 // rows per warp step in pass A
 // |v| < 2^vbits: five planes carry 39-bit values, four planes 31-bit values
 __host__ __device__ constexpr int oz_vbits(int nplanes) { return nplanes == 5 ? 38 : 30; }
@@ -243,9 +247,10 @@ __device__ __forceinline__ void oz_rows_fetch(const OzRowsArgs& a, int64_t batch
 // i + STAGES - 1 before the warp starts on batch i); no producer warp and no "empty" barriers are needed because the
 // warp that refills a stage is the one that has just finished reading it.
 template <int NP>
-__global__ void __launch_bounds__(OZ_ROWS_THREADS, 1)
+__global__ void __launch_bounds__(oz_rows_threads(NP), 1)
 k_oz_rows(const OzRowsArgs a) {
-  constexpr int NW = OZ_ROWS_THREADS / 32;
+  constexpr int THREADS = oz_rows_threads(NP);
+  constexpr int NW = THREADS / 32;
   constexpr int R = OZ_R;
   constexpr int NS = OZ_ROWS_STAGES;
   extern __shared__ __align__(128) double oz_ring[];          // [NW][NS][R][d]
@@ -253,12 +258,12 @@ k_oz_rows(const OzRowsArgs a) {
   __shared__ double s_g[OZ_COLS], s_u[OZ_COLS], s_sc[4];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t d = a.d, n = a.n;
-  for (int j = tid; j < OZ_COLS; j += OZ_ROWS_THREADS) { s_g[j] = 0.0; s_u[j] = 0.0; }
+  for (int j = tid; j < OZ_COLS; j += THREADS) { s_g[j] = 0.0; s_u[j] = 0.0; }
   if (tid < 4) s_sc[tid] = 0.0;
   // The inner loop reads whole 256-wide rows of its ring without guards: columns beyond d and rows beyond n take part in
   // the arithmetic with zero factors (beta, the column scale, the row's residual and weight are 0 there), so what they
   // read only has to be finite: the ring starts out as zeros and afterwards holds rows of X.
-  for (int j = tid; j < NW * NS * R * OZ_COLS; j += OZ_ROWS_THREADS) oz_ring[j] = 0.0;
+  for (int j = tid; j < NW * NS * R * OZ_COLS; j += THREADS) oz_ring[j] = 0.0;
   if (tid < NW * NS) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((unsigned)__cvta_generic_to_shared(&ring_full[tid / NS][tid % NS])));
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
@@ -467,7 +472,7 @@ k_oz_rows(const OzRowsArgs a) {
     __syncthreads();
   }
   double* out = a.partials + (size_t)blockIdx.x * (2 * d + 3);
-  for (int64_t j = tid; j < d; j += OZ_ROWS_THREADS) { out[j] = s_g[j]; out[d + j] = s_u[j]; }
+  for (int64_t j = tid; j < d; j += THREADS) { out[j] = s_g[j]; out[d + j] = s_u[j]; }
   if (tid == 0) { out[2 * d] = s_sc[0]; out[2 * d + 1] = s_sc[1]; out[2 * d + 2] = s_sc[2]; }
 }
 
@@ -966,18 +971,18 @@ int oz_gradient_rows(int device, int family, const double* x, int64_t n, int64_t
                      const double* beta, int skip_obj, double* parts, int max_parts, int* nparts, cudaStream_t st) {
   static KernelSetup setup;
   int occ = 1;
-  const size_t rows_smem = (size_t)(OZ_ROWS_THREADS / 32) * OZ_ROWS_STAGES * OZ_R * OZ_COLS * sizeof(double);
-  if (int rc = setup.get(device, k_oz_rows<0>, OZ_ROWS_THREADS, rows_smem, &occ)) return rc;
+  const size_t rows_smem = (size_t)(OZ_GRAD_THREADS / 32) * OZ_ROWS_STAGES * OZ_R * OZ_COLS * sizeof(double);
+  if (int rc = setup.get(device, k_oz_rows<0>, OZ_GRAD_THREADS, rows_smem, &occ)) return rc;
   OzRowsArgs ra;
   ra.x = x; ra.n = n; ra.d = d; ra.ldx = ldx; ra.y = y; ra.ydt = ydt; ra.beta = beta;
   ra.family = family; ra.skip_obj = skip_obj; ra.ew = 0; ra.prep = nullptr; ra.planes = nullptr; ra.plane_stride = 0;
   ra.flag = nullptr; ra.seed = 0; ra.partials = parts;
-  int64_t want = ((n + OZ_R - 1) / OZ_R + (OZ_ROWS_THREADS / 32) - 1) / (OZ_ROWS_THREADS / 32);
+  int64_t want = ((n + OZ_R - 1) / OZ_R + (OZ_GRAD_THREADS / 32) - 1) / (OZ_GRAD_THREADS / 32);
   int64_t grid = (int64_t)dev_info(device).sms * occ;
   if (grid > max_parts) grid = max_parts;
   if (grid > want) grid = want;
   if (grid < 1) grid = 1;
-  k_oz_rows<0><<<(unsigned)grid, OZ_ROWS_THREADS, rows_smem, st>>>(ra);
+  k_oz_rows<0><<<(unsigned)grid, OZ_GRAD_THREADS, rows_smem, st>>>(ra);
   NB_LAUNCH_CHECK();
   *nparts = (int)grid;
   return 0;
