@@ -32,12 +32,21 @@ struct CholArgs {
 constexpr int CH_T = 256;
 constexpr int CH_B = 32;
 
+// Everything that is serial here is kept short: the diagonal block is factorised by the whole CTA (one element per thread
+// and step, three block barriers per column), its inverse W = L_kk^-1 is formed once (one column per lane, in registers)
+// and stored in the unused strict upper triangle of the block, and from then on the panel below the block (X = A W^T), and
+// both substitutions at the end (z_k = W_k t_k), are products with no dependent chain of loads or divisions.  The first
+// version solved every row of a panel and every step of the substitutions by forward substitution against L_kk (32
+// dependent steps each, the substitutions with a trip to L2 per step): 0.79 ms at p = 257 against 28 grid barriers' worth
+// (~0.1 ms) of unavoidable latency.
 __global__ void __launch_bounds__(CH_T)
 k_chol_solve(const CholArgs a) {
   cg::grid_group grid = cg::this_grid();
-  __shared__ double sb[CH_B][CH_B + 1];
+  __shared__ double sb[CH_B][CH_B + 1];      // lower triangle: L_kk; strict upper triangle: W^T (sb[m][c] = W[c][m], m < c)
+  __shared__ double sorig[CH_B];
+  __shared__ int sbad;
   const int p = a.p;
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int gthreads = gridDim.x * CH_T, gtid = blockIdx.x * CH_T + tid;
   for (int e = gtid; e < p * p; e += gthreads) {
     const int i = e / p, j = e - i * p;
@@ -47,64 +56,86 @@ k_chol_solve(const CholArgs a) {
   grid.sync();
   for (int k0 = 0; k0 < p; k0 += CH_B) {
     const int nb = (p - k0 < CH_B) ? (p - k0) : CH_B;
-    // ---- diagonal block: CTA 0, one warp, lane = row
     if (blockIdx.x == 0) {
-      for (int e = tid; e < nb * nb; e += CH_T) {
-        const int r = e / nb, c = e - r * nb;
-        sb[r][c] = a.l[(size_t)(k0 + r) * p + k0 + c];
+      // ---- diagonal block: factorise, invert, store both
+      for (int e = tid; e < CH_B * CH_B; e += CH_T) {
+        const int r = e >> 5, c = e & 31;
+        sb[r][c] = (r < nb && c <= r) ? a.l[(size_t)(k0 + r) * p + k0 + c] : 0.0;
       }
+      if (tid < nb) sorig[tid] = a.h[(size_t)(k0 + tid) * p + k0 + tid];
+      if (tid == 0) sbad = 0;
       __syncthreads();
-      if (tid < 32) {
-        int bad = 0;
-        for (int j = 0; j < nb; ++j) {
-          const double djj = sb[j][j];
-          // a pivot that cancelled down to rounding noise (exactly singular H: LU would meet a zero pivot) is not
-          // trusted either: the pivoted inverse decides such cases, as it did before.  Uniform over the warp.
-          const double orig = a.h[(size_t)(k0 + j) * p + k0 + j];
-          if (!(djj > 1e-13 * fabs(orig))) { bad = j + 1; break; }
-          const double r = sqrt(djj);
-          __syncwarp();
-          if (lane == j) sb[j][j] = r;
-          if (lane > j && lane < nb) sb[lane][j] /= r;
-          __syncwarp();
-          if (lane > j && lane < nb) {
-            const double lij = sb[lane][j];
-            for (int c = j + 1; c <= lane; ++c) sb[lane][c] -= lij * sb[c][j];
-          }
-          __syncwarp();
+      for (int j = 0; j < nb; ++j) {
+        const double djj = sb[j][j];
+        // a pivot that cancelled down to rounding noise (exactly singular H: LU would meet a zero pivot) is not
+        // trusted either: the pivoted inverse decides such cases.  Uniform over the CTA.
+        if (!(djj > 1e-13 * fabs(sorig[j]))) { if (tid == 0) sbad = j + 1; break; }
+        const double r = sqrt(djj);
+        __syncthreads();
+        if (tid == j) sb[j][j] = r;
+        if (tid > j && tid < nb) sb[tid][j] /= r;
+        __syncthreads();
+        for (int e = tid; e < CH_B * CH_B; e += CH_T) {
+          const int i = e >> 5, c = e & 31;
+          if (c > j && c <= i && i < nb) sb[i][c] -= sb[i][j] * sb[c][j];
         }
-        if (bad && lane == 0) *a.flag = k0 + bad;
+        __syncthreads();
       }
       __syncthreads();
-      for (int e = tid; e < nb * nb; e += CH_T) {
-        const int r = e / nb, c = e - r * nb;
-        if (c <= r) a.l[(size_t)(k0 + r) * p + k0 + c] = sb[r][c];
+      if (sbad == 0) {
+        if (warp == 0 && lane < nb) {
+          // column `lane` of W = L_kk^-1 by forward substitution, kept in registers
+          double w[CH_B];
+#pragma unroll
+          for (int i = 0; i < CH_B; ++i) {
+            double v = 0.0;
+            if (i < nb && i >= lane) {
+              if (i == lane) v = 1.0 / sb[i][i];
+              else {
+                double acc = 0.0;
+#pragma unroll
+                for (int m = 0; m < i; ++m) if (m >= lane) acc = fma(sb[i][m], w[m], acc);
+                v = -acc / sb[i][i];
+              }
+            }
+            w[i] = v;
+          }
+#pragma unroll
+          for (int i = 0; i < CH_B; ++i) if (i > lane && i < nb) sb[lane][i] = w[i];
+        }
+        __syncthreads();
+        for (int e = tid; e < nb * nb; e += CH_T) {
+          const int r = e / nb, c = e - r * nb;
+          a.l[(size_t)(k0 + r) * p + k0 + c] = sb[r][c];
+        }
+      } else if (tid == 0) {
+        *a.flag = k0 + sbad;
       }
     }
     __threadfence();
     grid.sync();
     if (*(volatile int*)a.flag != 0) return;                   // not positive definite: the caller's inverse path runs
     if (k0 + nb >= p) break;
-    // ---- panel below the block: one row per thread, x L_kk^T = a_row  (nb == 32 here)
+    // ---- panel below the block (nb == 32 here): X = A W^T, one warp per row, lane = column
     for (int e = tid; e < CH_B * CH_B; e += CH_T) {
-      const int r = e / CH_B, c = e - r * CH_B;
+      const int r = e >> 5, c = e & 31;
       sb[r][c] = a.l[(size_t)(k0 + r) * p + k0 + c];
     }
     __syncthreads();
-    for (int i = k0 + CH_B + gtid; i < p; i += gthreads) {
-      double* row = a.l + (size_t)i * p + k0;
-      double x[CH_B];
+    {
+      const double wdiag = 1.0 / sb[lane][lane];
+      const int gwarps = gridDim.x * (CH_T / 32);
+      for (int i = k0 + CH_B + blockIdx.x * (CH_T / 32) + warp; i < p; i += gwarps) {
+        double* row = a.l + (size_t)i * p + k0;
+        const double av = row[lane];
+        double acc = 0.0;
 #pragma unroll
-      for (int c = 0; c < CH_B; ++c) x[c] = row[c];
-#pragma unroll
-      for (int c = 0; c < CH_B; ++c) {
-        double s = x[c];
-#pragma unroll
-        for (int m = 0; m < c; ++m) s -= x[m] * sb[c][m];
-        x[c] = s / sb[c][c];
+        for (int m = 0; m < CH_B; ++m) {
+          const double am = __shfl_sync(0xffffffffu, av, m);
+          if (m < lane) acc = fma(am, sb[m][lane], acc);
+        }
+        row[lane] = fma(av, wdiag, acc);
       }
-#pragma unroll
-      for (int c = 0; c < CH_B; ++c) row[c] = x[c];
     }
     __threadfence();
     grid.sync();
@@ -124,19 +155,25 @@ k_chol_solve(const CholArgs a) {
     grid.sync();
   }
   if (blockIdx.x != 0) return;
-  // ---- L z = g, L^T delta = z: blocked substitutions by CTA 0
+  // ---- L z = g, L^T delta = z by CTA 0: per block a product with W_k (warp 0), then the update of the rows it feeds
   for (int i = tid; i < p; i += CH_T) a.z[i] = a.g[i];
   __syncthreads();
   for (int k0 = 0; k0 < p; k0 += CH_B) {
     const int nb = (p - k0 < CH_B) ? (p - k0) : CH_B;
     if (tid < 32) {
-      double v = lane < nb ? a.z[k0 + lane] : 0.0;
-      for (int j = 0; j < nb; ++j) {
-        if (lane == j) v /= a.l[(size_t)(k0 + j) * p + k0 + j];
-        const double zj = __shfl_sync(0xffffffffu, v, j);
-        if (lane > j && lane < nb) v -= a.l[(size_t)(k0 + lane) * p + k0 + j] * zj;
+      // z_k = W_k t: lane r needs W[r][m], m <= r: column r of the block's upper storage, the diagonal inverted
+      double wr[CH_B];
+#pragma unroll
+      for (int m = 0; m < CH_B; ++m)
+        wr[m] = (lane < nb && m <= lane) ? a.l[(size_t)(k0 + m) * p + k0 + lane] : 0.0;
+      const double tv = lane < nb ? a.z[k0 + lane] : 0.0;
+      double acc = 0.0;
+#pragma unroll
+      for (int m = 0; m < CH_B; ++m) {
+        const double tm = __shfl_sync(0xffffffffu, tv, m);
+        if (m < lane) acc = fma(wr[m], tm, acc);
       }
-      if (lane < nb) a.z[k0 + lane] = v;
+      if (lane < nb) a.z[k0 + lane] = acc + tv / wr[lane];
     }
     __syncthreads();
     for (int i = k0 + nb + tid; i < p; i += CH_T) {
@@ -150,13 +187,19 @@ k_chol_solve(const CholArgs a) {
   for (int k0 = ((p - 1) / CH_B) * CH_B; k0 >= 0; k0 -= CH_B) {
     const int nb = (p - k0 < CH_B) ? (p - k0) : CH_B;
     if (tid < 32) {
-      double v = lane < nb ? a.z[k0 + lane] : 0.0;
-      for (int j = nb - 1; j >= 0; --j) {
-        if (lane == j) v /= a.l[(size_t)(k0 + j) * p + k0 + j];
-        const double dj = __shfl_sync(0xffffffffu, v, j);
-        if (lane < j) v -= a.l[(size_t)(k0 + j) * p + k0 + lane] * dj;
+      // delta_k = W_k^T z_k: lane c needs W[m][c], m >= c: row c of the block's upper storage (contiguous), diagonal inverted
+      double wc[CH_B];
+#pragma unroll
+      for (int m = 0; m < CH_B; ++m)
+        wc[m] = (lane < nb && m < nb && m >= lane) ? a.l[(size_t)(k0 + lane) * p + k0 + m] : 0.0;
+      const double zv = lane < nb ? a.z[k0 + lane] : 0.0;
+      double acc = 0.0;
+#pragma unroll
+      for (int m = 0; m < CH_B; ++m) {
+        const double zm = __shfl_sync(0xffffffffu, zv, m);
+        if (m > lane) acc = fma(wc[m], zm, acc);
       }
-      if (lane < nb) a.z[k0 + lane] = v;
+      if (lane < nb) a.z[k0 + lane] = acc + zv / wc[lane];
     }
     __syncthreads();
     for (int i = tid; i < k0; i += CH_T) {
