@@ -329,6 +329,54 @@ def test_hessian_int8_four_planes_row_chunks_and_foreign_scale(app, monkeypatch)
     assert np.all(np.isnan(st[: p * p].reshape(p, p)[:d, :d]))
 
 
+@pytest.mark.parametrize("planes", ["5", "4"])
+@pytest.mark.parametrize("n,d,chunk", [(4_000, 256, None), (1_153, 132, None), (63, 256, None), (150_001, 256, None),
+                                       (200_001, 200, 65_536)])
+def test_hessian_int8_linear_is_bit_exact(app, monkeypatch, planes, n, d, chunk):
+    """Linear family: w = 1, so every step of the int8 Hessian is integer or exactly representable arithmetic, and
+    oracle/int8_gram.py states the float64 result bit for bit -- column scales, rounding (with the dither byte of the
+    four-plane variant), balanced digits, the 8 / 9 / 11 plane products on the tensor path, levels, conversion back.
+    Ragged rows, a width below 256 (zero-padded planes), several accumulation ranges, row chunks (the dither seed of a
+    chunk is its first row / 64)."""
+    from nums_b200 import device as dv, fused
+    from oracle import int8_gram as ig
+    monkeypatch.setenv("NUMS_B200_INT8_PLANES", planes)
+    if chunk:
+        monkeypatch.setenv("NUMS_B200_OZ_CHUNK_ROWS", str(chunk))
+    rng = np.random.default_rng(41 + d)
+    X = rng.standard_normal((n, d)) * np.exp2(rng.integers(-6, 7, d))
+    if d > 140:
+        X[:, 140] = 0.0
+    y = rng.standard_normal(n)
+    Xd = dv.from_numpy(X, 0)
+    found = fused.glm_prepare(Xd)
+    flags = fused.int8_flags(found, n)
+    s = dv.to_numpy(fused.glm_stats(Xd, dv.from_numpy(y, 0), dv.from_numpy(np.zeros(d + 1), 0), "linear", True,
+                                    hessian="int8!"))
+    p = d + 1
+    H = s[: p * p].reshape(p, p)[:d, :d]
+    # the device rounds the chunk length up to whole accumulation ranges: ask it what it used
+    want = ig.exact_gram_linear(X, int(planes), bool(flags & fused.NB_GLM_INT8_NO_LEVEL5), chunk_rows=_device_chunk_rows(n, chunk, int(planes)))
+    assert np.array_equal(H, want)
+
+
+def _device_chunk_rows(n, chunk, planes):
+    """The chunk length oz_plan (csrc/glm_ozaki.cu) derives from NUMS_B200_OZ_CHUNK_ROWS: at most four chunks, each a whole
+    number of accumulation ranges; ranges of equal length over the lanes (a quarter of the CTA pairs)."""
+    if not chunk:
+        return None
+    import torch
+    lanes = max(1, (torch.cuda.get_device_properties(0).multi_processor_count // 2) // 4)
+    max_range = 65536 if planes == 4 else 32768
+    rounds = -(-n // (lanes * max_range))
+    per_lane = -(-n // (lanes * rounds))
+    rr = min(max(-(-per_lane // 128) * 128, 128), max_range)
+    if -(-n // chunk) > 4:
+        chunk = -(-n // 4)
+    chunk = -(-chunk // rr) * rr
+    return None if chunk >= n else chunk
+
+
 def test_hessian_int8_rejects_a_foreign_column_scale(app):
     """The digit split relies on the block's own column maxima.  Handing the kernel the scales of another block
     (values up to 1000x larger than prepared for) must not give a plausible Hessian: H comes back NaN."""

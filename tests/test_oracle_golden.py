@@ -218,3 +218,29 @@ def test_readme_iteration_counts():
     _, it = oglm.fit("logistic", r["X"], r["y"], int(r["row_block"]), solver="newton-cg", penalty="l2", lam=1.0 / 10)
     assert it == int(g["readme_20000_iters"]) == 8
     assert int(g["readme_1000000_iters"]) == 8      # what SURVEY.md 8(d) probed for the README's own size
+
+
+@pytest.mark.parametrize("nplanes,no_level5,bound", [(5, False, 2.0 ** -36), (5, True, 2.0 ** -30), (4, True, 8.0 * 2.0 ** (3 - 31))])
+def test_exact_int8_gram_restatement_against_float64(nplanes, no_level5, bound):
+    """oracle/int8_gram.py (the integer restatement of the device's digit pipeline for the linear family) against the
+    float64 Gram matrix X^T X of glms.py:318-327: within the error model of each variant, exactly symmetric, an
+    all-zero column gives exact zeros, and splitting the rows into chunks changes only the dither (four planes)."""
+    from oracle import int8_gram as ig
+    rng = np.random.default_rng(3)
+    n, d = 2500, 132
+    X = rng.standard_normal((n, d)) / 7.0
+    X[:, 3] = 0.0
+    G = X.T @ X
+    s = np.sqrt(np.maximum(np.diag(G), 1e-300))
+    s[3] = 1.0
+    H = ig.exact_gram_linear(X, nplanes, no_level5)
+    scale = bound / np.sqrt(n) if nplanes == 4 or no_level5 else bound
+    assert np.max(np.abs(H - G) / np.outer(s, s)) < scale
+    assert np.array_equal(H, H.T) and np.all(H[3] == 0.0) and np.all(H[:, 3] == 0.0)
+    Hc = ig.exact_gram_linear(X, nplanes, no_level5, chunk_rows=1024)
+    if nplanes == 5:
+        assert np.array_equal(H, Hc)
+    else:
+        assert np.max(np.abs(Hc - G) / np.outer(s, s)) < scale
+    planes = ig.digit_planes(X, nplanes)
+    assert planes.shape == (nplanes, n, d) and planes.min() >= -128 and planes.max() <= 127
