@@ -257,3 +257,31 @@ def test_bind_host_to_gpu_changes_nothing_without_a_gpu():
     else:
         assert got is None or set(got) <= before
         os.sched_setaffinity(0, before)
+
+
+def test_int8_flag_selection_thresholds():
+    """fused.int8_flags: level 5 is dropped and four planes are chosen only where their error models stay a fifth (a tenth)
+    below the 1e-10 bar; NUMS_B200_INT8_PLANES pins the plane count."""
+    import os
+    from nums_b200 import fused
+
+    class Found:
+        def __init__(self, r):
+            self.range_log2, self.bad = r, False
+
+    old = os.environ.pop("NUMS_B200_INT8_PLANES", None)
+    try:
+        small, big = fused.int8_flags(Found(3), 40_000), fused.int8_flags(Found(3), 12_500_000)
+        assert small & fused.NB_GLM_INT8_HESSIAN and not small & fused.NB_GLM_INT8_FOUR_PLANES
+        assert big & fused.NB_GLM_INT8_FOUR_PLANES and big & fused.NB_GLM_INT8_NO_LEVEL5
+        assert not fused.int8_flags(Found(3), 2_000_000) & fused.NB_GLM_INT8_FOUR_PLANES
+        assert fused.int8_flags(Found(3), 2_400_000) & fused.NB_GLM_INT8_FOUR_PLANES
+        assert not fused.int8_flags(Found(5), 12_500_000) & fused.NB_GLM_INT8_FOUR_PLANES       # heavier tails need more rows
+        os.environ["NUMS_B200_INT8_PLANES"] = "5"
+        assert not fused.int8_flags(Found(3), 12_500_000) & fused.NB_GLM_INT8_FOUR_PLANES
+        os.environ["NUMS_B200_INT8_PLANES"] = "4"
+        assert fused.int8_flags(Found(3), 1_000) & fused.NB_GLM_INT8_FOUR_PLANES
+    finally:
+        os.environ.pop("NUMS_B200_INT8_PLANES", None)
+        if old is not None:
+            os.environ["NUMS_B200_INT8_PLANES"] = old
